@@ -1,0 +1,353 @@
+"""ctypes binding of libcgs_b200.so (include/cgs_b200.h) and its registration as torch.ops.cgs_b200.*.
+
+There is no CPU fallback and no PyTorch/SDPA fallback: every function here raises if the CUDA
+library is missing or the tensors are not CUDA tensors of the expected dtype.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+from typing import Optional
+
+import torch
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG_DIR, "libcgs_b200.so")
+
+_c_void_p = ctypes.c_void_p
+_c_int = ctypes.c_int
+_c_ll = ctypes.c_longlong
+_c_float = ctypes.c_float
+
+# name -> argtypes; every function returns int. Must list every symbol of include/cgs_b200.h.
+_SIGNATURES = {
+    "cgs_attention_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 12 + [_c_float, _c_void_p],
+    "cgs_layernorm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_float, _c_void_p],
+    "cgs_add_layernorm_fwd": [_c_void_p] * 6 + [_c_ll, _c_int, _c_float, _c_void_p],
+    "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
+    "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
+    "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
+    "cgs_cfg_denoise_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
+                                              _c_ll, _c_ll, _c_void_p],
+    "cgs_sampler_step_euler": [_c_void_p, _c_void_p, _c_float, _c_float, _c_void_p, _c_ll, _c_void_p],
+    "cgs_sampler_step_dpmpp2m": [_c_void_p] * 3 + [_c_float] * 4 + [_c_void_p, _c_ll, _c_void_p],
+    "cgs_cfg_sampler_tail_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
+                                                   _c_int] + [_c_float] * 4 + [_c_void_p, _c_void_p,
+                                                                               _c_ll, _c_ll, _c_void_p],
+}
+EXPORTED_SYMBOLS = ["cgs_last_error", "cgs_abi_version", *_SIGNATURES.keys()]
+
+_lib = None
+_lib_lock = threading.Lock()
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+def load_library(path: Optional[str] = None) -> ctypes.CDLL:
+    """dlopen the C-ABI library and declare its prototypes. Raises if it is not built."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    with _lib_lock:
+        if _lib is not None and path is None:
+            return _lib
+        p = path or LIB_PATH
+        if not os.path.exists(p):
+            raise NativeLibraryError(
+                f"{p} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). There is no CPU or PyTorch fallback for this path.")
+        lib = ctypes.CDLL(p)
+        lib.cgs_last_error.restype = ctypes.c_char_p
+        lib.cgs_last_error.argtypes = []
+        lib.cgs_abi_version.restype = _c_int
+        lib.cgs_abi_version.argtypes = []
+        for name, argtypes in _SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = _c_int
+            fn.argtypes = argtypes
+        if path is None:
+            _lib = lib
+        return lib
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load_library().cgs_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (status {rc}): {msg}")
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _require_cuda(name: str, t: torch.Tensor, dtype: torch.dtype) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: expected a CUDA tensor, got device {t.device} "
+                           "(this path has no CPU fallback)")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name}: expected dtype {dtype}, got {t.dtype}")
+
+
+# ----------------------------------------------------------------------------------------------
+# attention
+# ----------------------------------------------------------------------------------------------
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> torch.Tensor:
+    """softmax(q k^T / sqrt(d)) v per head; q [B, Nq, heads*d], k/v [B, Nk, heads*d] -> [B, Nq, heads*d].
+
+    Same layout contract as the reference's optimized_attention (attention.py:337-349). Inputs may
+    be views with arbitrary batch/token strides (last dim contiguous), e.g. slices of a fused QKV.
+    """
+    for n, t in (("q", q), ("k", k), ("v", v)):
+        _require_cuda(f"attention {n}", t, torch.bfloat16)
+        if t.dim() != 3 or t.stride(2) != 1:
+            raise RuntimeError(f"attention {n}: expected [B, N, heads*d] with a contiguous last dim")
+    B, Nq, inner = q.shape
+    Nk = k.shape[1]
+    if inner % heads != 0 or k.shape[2] != inner or v.shape[2] != inner or k.shape[0] != B \
+            or v.shape[0] != B or v.shape[1] != Nk:
+        raise RuntimeError(f"attention: inconsistent shapes q{tuple(q.shape)} k{tuple(k.shape)} v{tuple(v.shape)}")
+    d = inner // heads
+    out = torch.empty((B, Nq, inner), dtype=torch.bfloat16, device=q.device)
+    if B == 0 or Nq == 0:
+        return out
+    rc = load_library().cgs_attention_fwd(
+        q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, heads, Nq, Nk, d,
+        q.stride(0), q.stride(1), d, k.stride(0), k.stride(1), d, v.stride(0), v.stride(1), d,
+        out.stride(0), out.stride(1), d, float(d) ** -0.5, _stream(q))
+    _check(rc, "cgs_attention_fwd")
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# LayerNorm
+# ----------------------------------------------------------------------------------------------
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
+    _require_cuda("layer_norm x", x, torch.bfloat16)
+    _require_cuda("layer_norm weight", weight, torch.bfloat16)
+    _require_cuda("layer_norm bias", bias, torch.bfloat16)
+    C = x.shape[-1]
+    xc = x if x.is_contiguous() else x.contiguous()
+    y = torch.empty_like(xc)
+    rows = xc.numel() // C if C else 0
+    rc = load_library().cgs_layernorm_fwd(xc.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+                                          rows, C, eps, _stream(x))
+    _check(rc, "cgs_layernorm_fwd")
+    return y
+
+
+def add_layer_norm_(x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor,
+                    eps: float = 1e-5) -> torch.Tensor:
+    """In place x += residual (bf16 rounding, like the reference), returns LN(x)."""
+    _require_cuda("add_layer_norm x", x, torch.bfloat16)
+    _require_cuda("add_layer_norm residual", residual, torch.bfloat16)
+    if not x.is_contiguous() or not residual.is_contiguous() or x.shape != residual.shape:
+        raise RuntimeError("add_layer_norm_: x and residual must be contiguous and of equal shape")
+    C = x.shape[-1]
+    y = torch.empty_like(x)
+    rows = x.numel() // C if C else 0
+    rc = load_library().cgs_add_layernorm_fwd(x.data_ptr(), residual.data_ptr(), weight.data_ptr(),
+                                              bias.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, eps,
+                                              _stream(x))
+    _check(rc, "cgs_add_layernorm_fwd")
+    return y
+
+
+# ----------------------------------------------------------------------------------------------
+# GEMMs
+# ----------------------------------------------------------------------------------------------
+def _as_2d(x: torch.Tensor) -> torch.Tensor:
+    x2 = x.reshape(-1, x.shape[-1])
+    if x2.stride(1) != 1:
+        x2 = x2.contiguous()
+    return x2
+
+
+def geglu(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """(x W_v^T + b_v) * gelu(x W_g^T + b_g) with weight [2N, K] = the reference's GEGLU.proj.weight."""
+    _require_cuda("geglu x", x, torch.bfloat16)
+    _require_cuda("geglu weight", weight, torch.bfloat16)
+    if bias is not None:
+        _require_cuda("geglu bias", bias, torch.bfloat16)
+    K = x.shape[-1]
+    N2, Kw = weight.shape
+    if Kw != K or N2 % 2 != 0 or weight.stride(1) != 1:
+        raise RuntimeError(f"geglu: weight {tuple(weight.shape)} does not match x[..., {K}]")
+    N = N2 // 2
+    x2 = _as_2d(x)
+    M = x2.shape[0]
+    y = torch.empty((*x.shape[:-1], N), dtype=torch.bfloat16, device=x.device)
+    rc = load_library().cgs_geglu_gemm_fwd(x2.data_ptr(), weight.data_ptr(),
+                                           bias.data_ptr() if bias is not None else None, y.data_ptr(),
+                                           M, N, K, x2.stride(0), weight.stride(0), N, _stream(x))
+    _check(rc, "cgs_geglu_gemm_fwd")
+    return y
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
+           residual: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x W^T (+ bias) (+ residual); `out` may be `residual` for the reference's in-place `x += n`."""
+    _require_cuda("linear x", x, torch.bfloat16)
+    _require_cuda("linear weight", weight, torch.bfloat16)
+    K = x.shape[-1]
+    N, Kw = weight.shape
+    if Kw != K or weight.stride(1) != 1:
+        raise RuntimeError(f"linear: weight {tuple(weight.shape)} does not match x[..., {K}]")
+    x2 = _as_2d(x)
+    M = x2.shape[0]
+    if out is None:
+        out = torch.empty((*x.shape[:-1], N), dtype=torch.bfloat16, device=x.device)
+    elif not out.is_contiguous() or out.shape[-1] != N or out.numel() != M * N:
+        raise RuntimeError("linear: `out` must be contiguous [..., N]")
+    r_ptr = None
+    if residual is not None:
+        _require_cuda("linear residual", residual, torch.bfloat16)
+        if not residual.is_contiguous() or residual.numel() != M * N:
+            raise RuntimeError("linear: `residual` must be contiguous [..., N]")
+        r_ptr = residual.data_ptr()
+    if bias is not None:
+        _require_cuda("linear bias", bias, torch.bfloat16)
+    rc = load_library().cgs_linear_fwd(x2.data_ptr(), weight.data_ptr(),
+                                       bias.data_ptr() if bias is not None else None, r_ptr,
+                                       out.data_ptr(), M, N, K, x2.stride(0), weight.stride(0), N, N,
+                                       _stream(x))
+    _check(rc, "cgs_linear_fwd")
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# CFG / sampler tail
+# ----------------------------------------------------------------------------------------------
+def _flat_f32(name: str, t: torch.Tensor) -> None:
+    _require_cuda(name, t, torch.float32)
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name}: must be contiguous")
+
+
+def unet_input(x: torch.Tensor, sigma: torch.Tensor, copies: int, sigma_data: float = 1.0) -> torch.Tensor:
+    """bf16(x / sqrt(sigma^2 + sigma_data^2)) repeated `copies` times along the batch."""
+    _flat_f32("unet_input x", x)
+    _flat_f32("unet_input sigma", sigma)
+    B = x.shape[0]
+    per = x.numel() // B if B else 0
+    out = torch.empty((copies * B, *x.shape[1:]), dtype=torch.bfloat16, device=x.device)
+    rc = load_library().cgs_unet_input_fwd(x.data_ptr(), sigma.data_ptr(), out.data_ptr(), B, per, copies,
+                                           sigma_data, _stream(x))
+    _check(rc, "cgs_unet_input_fwd")
+    return out
+
+
+def _model_out_ptrs(model_out_uncond, model_out_cond):
+    if model_out_cond.dtype not in (torch.bfloat16, torch.float32) or not model_out_cond.is_cuda:
+        raise RuntimeError("model output must be a CUDA bf16 or fp32 tensor")
+    if not model_out_cond.is_contiguous():
+        raise RuntimeError("model output must be contiguous")
+    is_bf16 = int(model_out_cond.dtype == torch.bfloat16)
+    u_ptr = None
+    if model_out_uncond is not None:
+        if model_out_uncond.dtype != model_out_cond.dtype or not model_out_uncond.is_contiguous():
+            raise RuntimeError("uncond/cond model outputs must share dtype and be contiguous")
+        u_ptr = model_out_uncond.data_ptr()
+    return u_ptr, model_out_cond.data_ptr(), is_bf16
+
+
+def cfg_denoise(x, model_out_uncond, model_out_cond, sigma, cond_scale: float, pred_type: int,
+                sigma_data: float = 1.0) -> torch.Tensor:
+    _flat_f32("cfg_denoise x", x)
+    _flat_f32("cfg_denoise sigma", sigma)
+    u_ptr, c_ptr, is_bf16 = _model_out_ptrs(model_out_uncond, model_out_cond)
+    B = x.shape[0]
+    per = x.numel() // B if B else 0
+    out = torch.empty_like(x)
+    rc = load_library().cgs_cfg_denoise_fwd(x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(),
+                                            cond_scale, pred_type, sigma_data, out.data_ptr(), B, per,
+                                            _stream(x))
+    _check(rc, "cgs_cfg_denoise_fwd")
+    return out
+
+
+def sampler_step_euler(x, denoised, sigma_hat: float, dt: float, out: Optional[torch.Tensor] = None):
+    _flat_f32("euler x", x)
+    _flat_f32("euler denoised", denoised)
+    out = torch.empty_like(x) if out is None else out
+    rc = load_library().cgs_sampler_step_euler(x.data_ptr(), denoised.data_ptr(), sigma_hat, dt,
+                                               out.data_ptr(), x.numel(), _stream(x))
+    _check(rc, "cgs_sampler_step_euler")
+    return out
+
+
+def sampler_step_dpmpp2m(x, denoised, old_denoised, c_x: float, c_d: float, c_cur: float, c_old: float,
+                         out: Optional[torch.Tensor] = None):
+    _flat_f32("dpmpp2m x", x)
+    _flat_f32("dpmpp2m denoised", denoised)
+    if old_denoised is not None:
+        _flat_f32("dpmpp2m old_denoised", old_denoised)
+    out = torch.empty_like(x) if out is None else out
+    rc = load_library().cgs_sampler_step_dpmpp2m(
+        x.data_ptr(), denoised.data_ptr(), old_denoised.data_ptr() if old_denoised is not None else None,
+        c_x, c_d, c_cur, c_old, out.data_ptr(), x.numel(), _stream(x))
+    _check(rc, "cgs_sampler_step_dpmpp2m")
+    return out
+
+
+def cfg_sampler_tail(x, model_out_uncond, model_out_cond, sigma, cond_scale: float, pred_type: int,
+                     old_denoised, sampler: int, c0: float, c1: float, c2: float, c3: float,
+                     sigma_data: float = 1.0, x_out: Optional[torch.Tensor] = None):
+    """One launch: model output -> denoised (CFG) -> sampler update. Returns (denoised, x_next)."""
+    _flat_f32("tail x", x)
+    _flat_f32("tail sigma", sigma)
+    u_ptr, c_ptr, is_bf16 = _model_out_ptrs(model_out_uncond, model_out_cond)
+    if old_denoised is not None:
+        _flat_f32("tail old_denoised", old_denoised)
+    B = x.shape[0]
+    per = x.numel() // B if B else 0
+    denoised = torch.empty_like(x)
+    x_next = torch.empty_like(x) if x_out is None else x_out
+    rc = load_library().cgs_cfg_sampler_tail_fwd(
+        x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(), cond_scale, pred_type, sigma_data,
+        old_denoised.data_ptr() if old_denoised is not None else None, sampler, c0, c1, c2, c3,
+        denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
+    _check(rc, "cgs_cfg_sampler_tail_fwd")
+    return denoised, x_next
+
+
+# ----------------------------------------------------------------------------------------------
+# torch.ops registration (namespace cgs_b200), with Meta kernels so shape tracing / fake tensors work
+# ----------------------------------------------------------------------------------------------
+_torch_lib = None
+
+
+def register_torch_ops() -> None:
+    global _torch_lib
+    if _torch_lib is not None:
+        return
+    lib = torch.library.Library("cgs_b200", "DEF")
+    lib.define("attention(Tensor q, Tensor k, Tensor v, int heads) -> Tensor")
+    lib.define("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps) -> Tensor")
+    lib.define("geglu(Tensor x, Tensor weight, Tensor? bias) -> Tensor")
+    lib.define("linear(Tensor x, Tensor weight, Tensor? bias, Tensor? residual) -> Tensor")
+    lib.define("cfg_denoise(Tensor x, Tensor? out_uncond, Tensor out_cond, Tensor sigma, float cond_scale, "
+               "int pred_type) -> Tensor")
+    lib.define("sampler_step_euler(Tensor x, Tensor denoised, float sigma_hat, float dt) -> Tensor")
+    lib.define("sampler_step_dpmpp2m(Tensor x, Tensor denoised, Tensor? old_denoised, float c_x, float c_d, "
+               "float c_cur, float c_old) -> Tensor")
+
+    lib.impl("attention", attention, "CUDA")
+    lib.impl("layer_norm", layer_norm, "CUDA")
+    lib.impl("geglu", geglu, "CUDA")
+    lib.impl("linear", lambda x, w, b, r: linear(x, w, b, r), "CUDA")
+    lib.impl("cfg_denoise", lambda x, u, c, s, cs, pt: cfg_denoise(x, u, c, s, cs, pt), "CUDA")
+    lib.impl("sampler_step_euler", lambda x, d, s, dt: sampler_step_euler(x, d, s, dt), "CUDA")
+    lib.impl("sampler_step_dpmpp2m",
+             lambda x, d, o, a, b, c, e: sampler_step_dpmpp2m(x, d, o, a, b, c, e), "CUDA")
+
+    lib.impl("attention", lambda q, k, v, heads: torch.empty_like(q), "Meta")
+    lib.impl("layer_norm", lambda x, w, b, eps: torch.empty_like(x), "Meta")
+    lib.impl("geglu", lambda x, w, b: x.new_empty((*x.shape[:-1], w.shape[0] // 2)), "Meta")
+    lib.impl("linear", lambda x, w, b, r: x.new_empty((*x.shape[:-1], w.shape[0])), "Meta")
+    lib.impl("cfg_denoise", lambda x, u, c, s, cs, pt: torch.empty_like(x), "Meta")
+    lib.impl("sampler_step_euler", lambda x, d, s, dt: torch.empty_like(x), "Meta")
+    lib.impl("sampler_step_dpmpp2m", lambda x, d, o, a, b, c, e: torch.empty_like(x), "Meta")
+    _torch_lib = lib

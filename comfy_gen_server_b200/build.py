@@ -1,0 +1,98 @@
+"""Build the C-ABI CUDA library (libcgs_b200.so) in-tree with nvcc for sm_100a.
+
+The library has no dependency on torch or libcuda at link time: launchers take raw pointers,
+sizes, strides and a cudaStream_t (as void*), and return an int status (include/cgs_b200.h).
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import shutil
+import subprocess
+import sys
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG_DIR, "csrc")
+LIB_PATH = os.path.join(PKG_DIR, "libcgs_b200.so")
+STAMP_PATH = os.path.join(PKG_DIR, ".libcgs_b200.stamp")
+
+SOURCES = ["common.cu", "layernorm.cu", "sampler_tail.cu", "geglu_gemm.cu", "attention.cu"]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo",
+    "-Xcompiler", "-fPIC",
+    "--expt-relaxed-constexpr",
+    "-Xptxas", "-v",
+]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found; the CUDA extension cannot be built")
+
+
+def _sources() -> list[str]:
+    return [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+
+
+def _digest() -> str:
+    h = hashlib.sha256()
+    for name in sorted(os.listdir(CSRC)):
+        if name.endswith((".cu", ".cuh", ".h")):
+            with open(os.path.join(CSRC, name), "rb") as f:
+                h.update(name.encode())
+                h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB_PATH) or not os.path.exists(STAMP_PATH):
+        return True
+    with open(STAMP_PATH) as f:
+        return f.read().strip() != _digest()
+
+
+def build(force: bool = False, verbose: bool = True) -> str:
+    """Compile every .cu into objects (in parallel) and link the shared library."""
+    if not force and not needs_build():
+        return LIB_PATH
+    nvcc = _nvcc()
+    obj_dir = os.path.join(PKG_DIR, "build")
+    os.makedirs(obj_dir, exist_ok=True)
+    procs = []
+    objs = []
+    for src in _sources():
+        obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
+        objs.append(obj)
+        cmd = [nvcc, *NVCC_FLAGS, "-I", CSRC, "-c", os.path.join(CSRC, src), "-o", obj]
+        procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    log_lines = []
+    failed = False
+    for src, p in procs:
+        out, _ = p.communicate()
+        log_lines.append(f"==== {src} (exit {p.returncode})\n{out}")
+        failed |= p.returncode != 0
+    log = "\n".join(log_lines)
+    with open(os.path.join(obj_dir, "nvcc.log"), "w") as f:
+        f.write(log)
+    if failed:
+        sys.stderr.write(log)
+        raise RuntimeError("nvcc failed; see output above")
+    link = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-lcudart"]
+    r = subprocess.run(link, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("link failed")
+    with open(STAMP_PATH, "w") as f:
+        f.write(_digest())
+    if verbose:
+        print(f"built {LIB_PATH}")
+    return LIB_PATH
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv)

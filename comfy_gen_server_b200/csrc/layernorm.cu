@@ -1,0 +1,157 @@
+// L1: LayerNorm over the channel dimension of token-major activations, bf16 in / bf16 out,
+// statistics in fp32 (two-pass in registers). Replaces the reference's ops.LayerNorm ->
+// F.layer_norm call (reference comfy/ops.py:97-113) used as norm1/norm2/norm3 of every
+// BasicTransformerBlock (reference comfy/ldm/modules/attention.py:450-453).
+//
+// Also the fused residual form  x <- x + r ; y <- LN(x)  which is the reference's
+// `x += n` (attention.py:527,567) followed by the next norm (attention.py:534,570) in one pass.
+//
+// HBM-bound: one warp per row, 16-byte loads kept in registers between the two passes, so each
+// element is read once and written once. Algorithmic bytes = 2 * rows * C * 2.
+#include "common.cuh"
+
+namespace cgs {
+
+struct alignas(16) Vec8 {
+    __nv_bfloat162 v[4];
+};
+
+__device__ __forceinline__ Vec8 ld_stream(const Vec8* p) {
+    Vec8 r;
+    uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3])
+                 : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// MAXV = max 16-byte vectors per lane  (C <= 256 * MAXV).
+template <int MAXV, bool ADD_RESIDUAL>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
+                 const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
+                 __nv_bfloat16* x_out, __nv_bfloat16* __restrict__ y, long long rows,
+                 int C, float eps) {
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nvec = C >> 3;
+    const Vec8* xr = reinterpret_cast<const Vec8*>(x + row * C);
+    const Vec8* rr = ADD_RESIDUAL ? reinterpret_cast<const Vec8*>(res + row * C) : nullptr;
+
+    float f[MAXV][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int v = lane + i * 32;
+        if (v < nvec) {
+            // x_out may alias x (in-place residual update): plain loads on that path.
+            Vec8 a = ADD_RESIDUAL ? xr[v] : ld_stream(xr + v);
+            if (ADD_RESIDUAL) {
+                Vec8 b = rr[v];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    // the reference adds in bf16 (x += n on bf16 tensors): round the sum to bf16
+                    // before normalising, and store it as the new residual stream.
+                    a.v[j] = __hadd2_rn(a.v[j], b.v[j]);
+                }
+                reinterpret_cast<Vec8*>(x_out + row * C)[v] = a;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float2 t = __bfloat1622float2(a.v[j]);
+                f[i][2 * j] = t.x;
+                f[i][2 * j + 1] = t.y;
+                sum += t.x + t.y;
+            }
+        }
+    }
+    const float mean = warp_sum(sum) / (float)C;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        if (lane + i * 32 < nvec) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float d = f[i][j] - mean;
+                sq += d * d;
+            }
+        }
+    }
+    const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+
+    const Vec8* g8 = reinterpret_cast<const Vec8*>(gamma);
+    const Vec8* b8 = reinterpret_cast<const Vec8*>(beta);
+    Vec8* yr = reinterpret_cast<Vec8*>(y + row * C);
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int v = lane + i * 32;
+        if (v < nvec) {
+            Vec8 g = g8[v];
+            Vec8 b = b8[v];
+            Vec8 o;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 gg = __bfloat1622float2(g.v[j]);
+                const float2 bb = __bfloat1622float2(b.v[j]);
+                const float o0 = (f[i][2 * j] - mean) * rstd * gg.x + bb.x;
+                const float o1 = (f[i][2 * j + 1] - mean) * rstd * gg.y + bb.y;
+                o.v[j] = __floats2bfloat162_rn(o0, o1);
+            }
+            yr[v] = o;
+        }
+    }
+}
+
+template <bool ADD>
+static int launch_ln(const void* x, const void* res, const void* gamma, const void* beta,
+                     void* x_out, void* y, long long rows, int C, float eps, cudaStream_t stream) {
+    if (rows <= 0) return kOk;
+    if (C <= 0 || (C & 7) != 0) {
+        set_last_error("layernorm: C=%d must be a positive multiple of 8", C);
+        return kUnsupportedShape;
+    }
+    if (C > 2560) {
+        set_last_error("layernorm: C=%d exceeds the supported maximum of 2560", C);
+        return kUnsupportedShape;
+    }
+    const int warps = 8;
+    const unsigned grid = (unsigned)((rows + warps - 1) / warps);
+    auto xp = static_cast<const __nv_bfloat16*>(x);
+    auto rp = static_cast<const __nv_bfloat16*>(res);
+    auto gp = static_cast<const __nv_bfloat16*>(gamma);
+    auto bp = static_cast<const __nv_bfloat16*>(beta);
+    auto xo = static_cast<__nv_bfloat16*>(x_out);
+    auto yp = static_cast<__nv_bfloat16*>(y);
+    if (C <= 512)
+        layernorm_kernel<2, ADD><<<grid, warps * 32, 0, stream>>>(xp, rp, gp, bp, xo, yp, rows, C, eps);
+    else if (C <= 768)
+        layernorm_kernel<3, ADD><<<grid, warps * 32, 0, stream>>>(xp, rp, gp, bp, xo, yp, rows, C, eps);
+    else if (C <= 1280)
+        layernorm_kernel<5, ADD><<<grid, warps * 32, 0, stream>>>(xp, rp, gp, bp, xo, yp, rows, C, eps);
+    else
+        layernorm_kernel<10, ADD><<<grid, warps * 32, 0, stream>>>(xp, rp, gp, bp, xo, yp, rows, C, eps);
+    CGS_CUDA_CHECK(cudaGetLastError());
+    return kOk;
+}
+
+}  // namespace cgs
+
+extern "C" int cgs_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y,
+                                 long long rows, int C, float eps, void* stream) {
+    return cgs::launch_ln<false>(x, nullptr, gamma, beta, nullptr, y, rows, C, eps,
+                                 static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int cgs_add_layernorm_fwd(const void* x, const void* residual, const void* gamma,
+                                     const void* beta, void* x_out, void* y, long long rows, int C,
+                                     float eps, void* stream) {
+    return cgs::launch_ln<true>(x, residual, gamma, beta, x_out, y, rows, C, eps,
+                                static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,159 @@
+/*
+ * cgs_b200.h -- C-ABI of libcgs_b200.so: the B200 (sm_100a) kernels for the per-step UNet denoise
+ * hot path of the ComfyUI-derived Comfy-Gen-Server.
+ *
+ * The reference is pure Python/PyTorch and has no FFI of its own; every entry point below
+ * replaces a PyTorch library call made by the reference at the cited file:line (paths relative
+ * to the reference tree). The Python boundary (comfy_gen_server_b200/_native.py) binds these
+ * with ctypes and registers them as torch.ops.cgs_b200.*; INTEGRATION.md shows the binding a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers on the current device;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - return value: 0 = ok, non-zero = error (enum below); cgs_last_error() returns a
+ *     thread-local human-readable message for the last non-zero return;
+ *   - no entry point allocates device memory, synchronises the device, or copies to the host;
+ *   - bf16 tensors are CUDA __nv_bfloat16; "elements" means bf16/float elements, not bytes;
+ *   - inputs are borrowed and never modified, outputs are fully overwritten (rows/columns the
+ *     sizes exclude are never touched).
+ */
+#ifndef CGS_B200_H
+#define CGS_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum cgs_status {
+    CGS_OK = 0,
+    CGS_BAD_ARGUMENT = 1,
+    CGS_UNSUPPORTED_SHAPE = 2,
+    CGS_CUDA_ERROR = 3,
+    CGS_DRIVER_ENTRY_MISSING = 4,
+    CGS_SCRATCH_TOO_SMALL = 5
+};
+
+/* Thread-local message describing the last non-zero status returned on this thread. */
+const char* cgs_last_error(void);
+int cgs_abi_version(void);
+
+/*
+ * Attention forward (A1 self-attention, A2 77/154-key cross-attention; same entry point).
+ * Replaces optimized_attention(q, k, v, heads, mask=None) == attention_pytorch ->
+ * F.scaled_dot_product_attention   (comfy/ldm/modules/attention.py:337-349, 352-368, 412).
+ *   q [B, Nq, H, d], k/v [B, Nk, H, d], out [B, Nq, H, d]; bf16; d contiguous, every stride a
+ *   multiple of 8 elements; d a multiple of 8, <= 192. softmax_scale is 1/sqrt(d) for the
+ *   reference's call. Non-causal, no mask, no dropout. fp32 accumulation and softmax.
+ */
+int cgs_attention_fwd(const void* q, const void* k, const void* v, void* out,
+                      int B, int H, int Nq, int Nk, int d,
+                      long long q_stride_b, long long q_stride_n, long long q_stride_h,
+                      long long k_stride_b, long long k_stride_n, long long k_stride_h,
+                      long long v_stride_b, long long v_stride_n, long long v_stride_h,
+                      long long o_stride_b, long long o_stride_n, long long o_stride_h,
+                      float softmax_scale, void* stream);
+
+/*
+ * LayerNorm forward (L1). Replaces ops.LayerNorm.forward -> F.layer_norm
+ * (comfy/ops.py:97-113) as norm1/norm2/norm3 (comfy/ldm/modules/attention.py:450-453).
+ *   x, y [rows, C] bf16 contiguous; gamma, beta [C] bf16; C multiple of 8, <= 2560;
+ *   fp32 statistics, eps as given (the reference uses torch's default 1e-5).
+ */
+int cgs_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y,
+                      long long rows, int C, float eps, void* stream);
+
+/*
+ * Residual add + LayerNorm in one pass: x_out = bf16(x + residual); y = LN(x_out).
+ * Replaces `x += n` followed by the next norm (comfy/ldm/modules/attention.py:527+534,
+ * 567+570). x_out may alias x (in-place update, as the reference does).
+ */
+int cgs_add_layernorm_fwd(const void* x, const void* residual, const void* gamma,
+                          const void* beta, void* x_out, void* y,
+                          long long rows, int C, float eps, void* stream);
+
+/*
+ * GEGLU projection (G1): y[m, n] = (x W^T + b)[m, n] * gelu_erf((x W^T + b)[m, N + n]).
+ * Replaces GEGLU.forward: Linear -> chunk(2) -> F.gelu -> mul
+ * (comfy/ldm/modules/attention.py:56-63).
+ *   x [M, K] (lda), W [2N, K] (ldw; rows [0,N) value half, [N,2N) gate half, exactly the
+ *   reference's proj.weight), bias [2N] or NULL, y [M, N] (ldy); bf16; K, lda, ldw, ldy
+ *   multiples of 8; N multiple of 128.
+ */
+int cgs_geglu_gemm_fwd(const void* x, const void* w, const void* bias, void* y,
+                       long long M, int N, int K,
+                       long long lda, long long ldw, long long ldy, void* stream);
+
+/*
+ * Linear: y = x W^T (+ bias) (+ residual). Replaces ops.Linear.forward -> F.linear
+ * (comfy/ops.py:40-52) for to_q/to_k/to_v/to_out/ff.net.2/proj_in/proj_out, optionally with
+ * the block's in-place residual add fused (comfy/ldm/modules/attention.py:527,567,572).
+ *   x [M, K], W [N, K], bias [N] or NULL, residual [M, N] (ldr) or NULL, y [M, N]; bf16;
+ *   N multiple of 32; y may alias residual.
+ */
+int cgs_linear_fwd(const void* x, const void* w, const void* bias, const void* residual, void* y,
+                   long long M, int N, int K,
+                   long long lda, long long ldw, long long ldy, long long ldr, void* stream);
+
+/*
+ * UNet input scaling: out[c, b, :] = bf16(x[b, :] / sqrt(sigma[b]^2 + sigma_data^2)), c < copies.
+ * Replaces EPS.calculate_input (comfy/model_sampling.py:6-8), the dtype cast
+ * (comfy/model_base.py:86-88) and the cond/uncond torch.cat (comfy/samplers.py:187).
+ *   x [batch, per_sample] fp32; sigma [batch] fp32; out [copies, batch, per_sample] bf16.
+ */
+int cgs_unet_input_fwd(const float* x, const float* sigma, void* out_bf16,
+                       long long batch, long long per_sample, int copies,
+                       float sigma_data, void* stream);
+
+/*
+ * eps/v -> denoised, then CFG combine (C1).
+ * Replaces EPS/V_PREDICTION.calculate_denoised (comfy/model_sampling.py:10-12, 27-29), the
+ * calc_cond_batch accumulate/divide with full-frame conds (comfy/samplers.py:220-226) and
+ * cfg_function's default branch (comfy/samplers.py:240).
+ *   denoised = D_u + (D_c - D_u) * cond_scale; out_uncond may be NULL (then denoised = D_c).
+ *   x, denoised [batch, per_sample] fp32; model outputs bf16 (out_is_bf16 = 1) or fp32;
+ *   sigma [batch] fp32; pred_type 0 = EPS, 1 = V_PREDICTION. Bit-identical to the reference's
+ *   fp32 eager composition.
+ */
+int cgs_cfg_denoise_fwd(const float* x, const void* out_uncond, const void* out_cond,
+                        int out_is_bf16, const float* sigma, float cond_scale, int pred_type,
+                        float sigma_data, float* denoised,
+                        long long batch, long long per_sample, void* stream);
+
+/*
+ * Euler update (S1): x_next = x + (x - denoised) / sigma_hat * dt.
+ * Replaces to_d + the Euler step of sample_euler (comfy/k_diffusion/sampling.py:45-47,137-143).
+ * x_next may alias x.
+ */
+int cgs_sampler_step_euler(const float* x, const float* denoised, float sigma_hat, float dt,
+                           float* x_next, long long n, void* stream);
+
+/*
+ * DPM-Solver++(2M) update (S1): x_next = c_x*x - c_d*(c_cur*denoised - c_old*old_denoised),
+ * or c_x*x - c_d*denoised when old_denoised is NULL (first step / last step).
+ * Replaces the update of sample_dpmpp_2m (comfy/k_diffusion/sampling.py:583-592); the
+ * coefficients are the reference's sigma_fn(t_next)/sigma_fn(t), (-h).expm1(), 1 + 1/(2r),
+ * 1/(2r), computed by the host once per schedule. x_next may alias x.
+ */
+int cgs_sampler_step_dpmpp2m(const float* x, const float* denoised, const float* old_denoised,
+                             float c_x, float c_d, float c_cur, float c_old,
+                             float* x_next, long long n, void* stream);
+
+/*
+ * The whole tail in one launch: model output -> denoised (CFG) -> sampler update.
+ *   sampler 1 = Euler (c0 = sigma_hat, c1 = dt); 2 = DPM++2M single-term form (c0 = c_x,
+ *   c1 = c_d); 3 = DPM++2M two-term form (c0..c3 = c_x, c_d, c_cur, c_old; old_denoised
+ *   required). Writes denoised and x_next; x_next may alias x; denoised must not alias
+ *   old_denoised.
+ */
+int cgs_cfg_sampler_tail_fwd(const float* x, const void* out_uncond, const void* out_cond,
+                             int out_is_bf16, const float* sigma, float cond_scale,
+                             int pred_type, float sigma_data, const float* old_denoised,
+                             int sampler, float c0, float c1, float c2, float c3,
+                             float* denoised, float* x_next,
+                             long long batch, long long per_sample, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CGS_B200_H */
