@@ -38,7 +38,7 @@ SDXL = {'use_checkpoint': False, 'image_size': 32, 'out_channels': 4, 'use_spati
 TINY_SD15 = {'use_checkpoint': False, 'image_size': 32, 'out_channels': 4, 'use_spatial_transformer': True,
              'legacy': False, 'adm_in_channels': None, 'in_channels': 4, 'model_channels': 64,
              'num_res_blocks': [1, 1], 'transformer_depth': [1, 1], 'channel_mult': [1, 2],
-             'transformer_depth_middle': 1, 'use_linear_in_transformer': False, 'context_dim': 96, 'num_heads': 2,
+             'transformer_depth_middle': 1, 'use_linear_in_transformer': False, 'context_dim': 96, 'num_heads': 8,
              'transformer_depth_output': [1, 1, 1, 1], 'use_temporal_attention': False,
              'use_temporal_resblock': False}
 

@@ -1,0 +1,267 @@
+"""Generate tests/golden/*.npz by running the REFERENCE ITSELF (imported from /root/reference, CPU, fp32).
+
+Run in the build container only (the reference does not exist on the GPU box):
+    python oracle/make_golden.py [--skip-sd15]
+
+The reference's own tests hold no golden vectors for this path, so these
+fixtures -- outputs of the reference's functions on seeded inputs -- are what pins the oracle
+(tests/test_oracle_golden.py) and, through it and directly, the CUDA path (tests -m gpu).
+Nothing is copied from the reference: it is imported, called, and its outputs are saved.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get("CGS_REFERENCE", "/root/reference")
+GOLD = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, REF)
+
+# shims documented in SURVEY.md section 8c
+sys.modules["torchsde"] = types.ModuleType("torchsde")
+import comfy.cli_args  # noqa: E402
+comfy.cli_args.args.cpu = True
+import comfy.model_management  # noqa: E402,F401
+import comfy.ops  # noqa: E402
+import comfy.utils  # noqa: E402
+import comfy.model_base as mb  # noqa: E402
+import comfy.model_detection as md  # noqa: E402
+import comfy.model_patcher  # noqa: E402
+import comfy.sample  # noqa: E402
+import comfy.samplers  # noqa: E402
+import comfy.model_sampling  # noqa: E402
+import comfy.k_diffusion.sampling as kds  # noqa: E402
+import comfy.ldm.modules.attention as ra  # noqa: E402
+
+from comfy_gen_server_b200 import unet_config as uc  # noqa: E402
+
+comfy.utils.PROGRESS_BAR_ENABLED = False
+OPS = comfy.ops.disable_weight_init
+
+
+def randn(shape, seed, scale=1.0):
+    return torch.randn(shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+
+def save(name, **arrays):
+    os.makedirs(GOLD, exist_ok=True)
+    path = os.path.join(GOLD, name + ".npz")
+    np.savez_compressed(path, **{k: (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v))
+                                 for k, v in arrays.items()})
+    print(f"wrote {path} ({os.path.getsize(path) / 1024:.1f} KiB)")
+
+
+def module_weights(module, seed):
+    shapes = {k: tuple(v.shape) for k, v in module.state_dict().items()}
+    sd = uc.seeded_state_dict(shapes, seed)
+    module.load_state_dict(sd)
+    return sd
+
+
+# ----------------------------------------------------------------------------------------------
+def gen_attention():
+    out = {}
+    cases = {"self_d64": (2, 64, 64, 2, 64), "cross77_d40": (2, 96, 77, 2, 40), "cross154_d80": (1, 50, 154, 3, 80),
+             "self_d160_ragged": (1, 72, 72, 2, 160)}
+    for name, (b, nq, nk, h, d) in cases.items():
+        q, k, v = randn((b, nq, h * d), 1), randn((b, nk, h * d), 2), randn((b, nk, h * d), 3)
+        o_basic = ra.attention_basic(q, k, v, h)
+        o_torch = ra.attention_pytorch(q, k, v, h)
+        assert (o_basic - o_torch).abs().max() < 1e-5
+        out.update({f"{name}.q": q, f"{name}.k": k, f"{name}.v": v, f"{name}.out": o_torch,
+                    f"{name}.heads": np.int64(h)})
+    save("attention", **out)
+
+
+def gen_blocks():
+    dim, heads, dh, ctx_dim = 128, 2, 64, 96
+    x = randn((2, 64, dim), 10)
+    ctx = randn((2, 77, ctx_dim), 11)
+    out = {"x": x, "context": ctx, "dim": np.int64(dim), "heads": np.int64(heads), "ctx_dim": np.int64(ctx_dim)}
+
+    ln = OPS.LayerNorm(dim)
+    module_weights(ln, 100)
+    out["layernorm.out"] = ln(x)
+
+    g = ra.GEGLU(dim, dim * 4, operations=OPS)
+    module_weights(g, 101)
+    out["geglu.out"] = g(x)
+
+    ff = ra.FeedForward(dim, glu=True, operations=OPS)
+    module_weights(ff, 102)
+    out["ff.out"] = ff(x)
+
+    ca = ra.CrossAttention(dim, context_dim=ctx_dim, heads=heads, dim_head=dh, operations=OPS)
+    module_weights(ca, 103)
+    out["cross_attention.out"] = ca(x, ctx)
+
+    blk = ra.BasicTransformerBlock(dim, heads, dh, context_dim=ctx_dim, checkpoint=False, operations=OPS)
+    module_weights(blk, 104)
+    out["block.out"] = blk(x.clone(), context=ctx, transformer_options={})
+
+    img = randn((2, dim, 8, 8), 12)
+    out["image"] = img
+    for use_linear in (False, True):
+        st = ra.SpatialTransformer(dim, heads, dh, depth=2, context_dim=ctx_dim, use_linear=use_linear,
+                                   use_checkpoint=False, operations=OPS)
+        module_weights(st, 105)
+        out[f"spatial_transformer.linear{int(use_linear)}.out"] = st(img.clone(), ctx, transformer_options={})
+    save("blocks", **out)
+
+
+def gen_schedules():
+    ms = comfy.model_sampling.ModelSamplingDiscrete()
+    out = {"sigmas_table": ms.sigmas}
+    for sched, steps in (("karras", 30), ("normal", 20), ("simple", 20), ("sgm_uniform", 20), ("karras", 7),
+                         ("normal", 25)):
+        out[f"{sched}_{steps}"] = comfy.samplers.calculate_sigmas(ms, sched, steps)
+    k30 = out["karras_30"]
+    out["timestep_karras_30"] = ms.timestep(k30[:-1])
+    out["sigma_of_t"] = ms.sigma(torch.tensor([0.0, 0.5, 10.25, 998.9, 999.0]))
+    sig = torch.tensor([0.5, 3.0])
+    x = randn((2, 4, 8, 8), 20)
+    eps = randn((2, 4, 8, 8), 21)
+    out["ci.sigma"], out["ci.x"], out["ci.model_out"] = sig, x, eps
+    out["calculate_input"] = comfy.model_sampling.EPS.calculate_input(ms, sig, x)
+    out["denoised_eps"] = comfy.model_sampling.EPS.calculate_denoised(ms, sig, eps, x)
+    out["denoised_v"] = comfy.model_sampling.V_PREDICTION.calculate_denoised(ms, sig, eps, x)
+    save("schedules", **out)
+
+
+def gen_sampler_kat():
+    ms = comfy.model_sampling.ModelSamplingDiscrete()
+    out = {}
+    for sampler, sched, steps in (("euler", "normal", 20), ("dpmpp_2m", "karras", 30), ("euler", "karras", 7),
+                                  ("dpmpp_2m", "normal", 25)):
+        sigmas = comfy.samplers.calculate_sigmas(ms, sched, steps)
+        x0 = randn((2, 4, 8, 8), 0) * sigmas[0]
+        trace = []
+        model = lambda x, sigma, **kw: x / (1.0 + sigma.view(-1, 1, 1, 1) ** 2)
+        fn = getattr(kds, "sample_" + sampler)
+        xf = fn(model, x0.clone(), sigmas, extra_args={}, callback=lambda d: trace.append(d["denoised"].clone()),
+                disable=True)
+        key = f"{sampler}_{sched}_{steps}"
+        out[key + ".x0"], out[key + ".final"], out[key + ".sigmas"] = x0, xf, sigmas
+        out[key + ".denoised_last"] = trace[-1]
+        const = fn(lambda x, s, **kw: torch.full_like(x, 0.25), x0.clone(), sigmas, extra_args={}, disable=True)
+        assert (const - 0.25).abs().max() == 0.0
+    save("sampler_kat", **out)
+
+
+class _StubModel:
+    """Records what calc_cond_batch feeds apply_model; returns a deterministic function of its inputs."""
+    def __init__(self):
+        self.calls = []
+
+    def memory_required(self, shape):
+        return 0
+
+    def apply_model(self, x, t, c_crossattn=None, transformer_options=None, **kw):
+        self.calls.append({"x": tuple(x.shape), "ctx": tuple(c_crossattn.shape),
+                           "cond_or_uncond": list(transformer_options["cond_or_uncond"])})
+        return x * 0.5 + c_crossattn.mean(dim=(1, 2)).view(-1, 1, 1, 1) + t.view(-1, 1, 1, 1) * 0.01
+
+
+def gen_cfg():
+    import comfy.conds
+    x = randn((2, 4, 8, 8), 30)
+    sigma = torch.tensor([2.5, 2.5])
+    cpos, cneg = randn((1, 77, 32), 31), randn((1, 154, 32), 32)
+    mk = lambda c: [{"model_conds": {"c_crossattn": comfy.conds.CONDCrossAttn(c)}}]
+    stub = _StubModel()
+    out_cfg = comfy.samplers.sampling_function(stub, x, sigma, mk(cneg), mk(cpos), 7.0, model_options={})
+    assert stub.calls[0]["cond_or_uncond"] == [1, 0] and stub.calls[0]["ctx"] == (4, 154, 32)
+    stub1 = _StubModel()
+    out_1 = comfy.samplers.sampling_function(stub1, x, sigma, mk(cneg), mk(cpos), 1.0, model_options={})
+    assert stub1.calls[0]["cond_or_uncond"] == [0]
+    cp, up = randn((2, 4, 8, 8), 33), randn((2, 4, 8, 8), 34)
+    save("cfg", x=x, sigma=sigma, cond=cpos, uncond=cneg, out_cfg7=out_cfg, out_cfg1=out_1,
+         cond_pred=cp, uncond_pred=up, cfg_function=comfy.samplers.cfg_function(None, cp, up, 7.0, x, sigma),
+         batch_order=np.array(stub.calls[0]["cond_or_uncond"]), batch_ctx_shape=np.array(stub.calls[0]["ctx"]))
+
+
+# ----------------------------------------------------------------------------------------------
+def build_reference_model(family: str, seed: int):
+    fam = uc.FAMILIES[family]
+    cfg = dict(fam["unet"])
+    cfg["dtype"] = torch.float32
+    mc = md.model_config_from_unet_config(dict(cfg))
+    if mc is None:  # tiny configs are not in the reference's supported list: wrap the closest family
+        import comfy.supported_models as sm
+        base = {"tiny_sd15": sm.SD15, "tiny_sd21v": sm.SD20, "tiny_sdxl": sm.SDXL}[family]
+        mc = base(dict(cfg))
+    mc.set_inference_dtype(torch.float32, None)
+    dev = torch.device("cpu")
+    if fam["prediction"] == "v":
+        model = mb.BaseModel(mc, model_type=mb.ModelType.V_PREDICTION, device=dev)
+    elif fam["adm"]:
+        model = mb.SDXL(mc, model_type=mb.ModelType.EPS, device=dev)
+    else:
+        model = mb.BaseModel(mc, model_type=mb.ModelType.EPS, device=dev)
+    shapes = {k: tuple(v.shape) for k, v in model.diffusion_model.state_dict().items()}
+    assert shapes == uc.param_shapes(fam["unet"]), "param_shapes diverged from the reference UNet"
+    model.diffusion_model.load_state_dict(uc.seeded_state_dict(shapes, seed))
+    return comfy.model_patcher.ModelPatcher(model, load_device=dev, offload_device=dev), model
+
+
+def gen_e2e(family, seed, batch, hw, steps, sampler, scheduler, pos_len, neg_len, name, record_steps=True):
+    fam = uc.FAMILIES[family]
+    ctx_dim = fam["unet"]["context_dim"]
+    patcher, model = build_reference_model(family, seed)
+    latent = torch.zeros(batch, 4, hw, hw)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    pos, neg = randn((1, pos_len, ctx_dim), seed + 1), randn((1, neg_len, ctx_dim), seed + 2)
+    pp, pn = randn((1, 1280), seed + 3), randn((1, 1280), seed + 4)
+    positive = [[pos, {"pooled_output": pp}]]
+    negative = [[neg, {"pooled_output": pn}]]
+    den = []
+    cb = (lambda i, denoised, x, total: den.append(denoised.clone())) if record_steps else None
+    t0 = time.time()
+    with torch.inference_mode():
+        out = comfy.sample.sample(patcher, noise, steps, 7.0, sampler, scheduler, positive, negative, latent,
+                                  seed=seed, disable_pbar=True, callback=cb)
+        # one raw UNet evaluation at the first sigma, to pin the network separately from the sampler
+        sig0 = comfy.samplers.calculate_sigmas(model.model_sampling, scheduler, steps)[0]
+        x0 = model.model_sampling.noise_scaling(sig0, noise.clone(), latent, True)
+        kw = {}
+        if fam["adm"]:
+            kw["y"] = model.encode_adm(pooled_output=pp, width=hw * 8, height=hw * 8, device="cpu")
+            kw["y"] = kw["y"].repeat(batch, 1)
+        d0 = model.apply_model(x0, sig0 * torch.ones(batch), c_crossattn=pos.repeat(batch, 1, 1),
+                               transformer_options={}, **kw)
+    dt = time.time() - t0
+    print(f"{name}: reference ran {steps} steps in {dt:.1f}s; out std {out.std():.4f} mean {out.mean():.4f} "
+          f"cond-denoised(step0) std {d0.std():.4f}")
+    arrays = dict(final=out, noise=noise, positive=pos, negative=neg, pooled_pos=pp, pooled_neg=pn,
+                  seed=np.int64(seed), steps=np.int64(steps), cond_denoised_step0=d0,
+                  ref_seconds=np.float64(dt), ref_threads=np.int64(torch.get_num_threads()))
+    if record_steps:
+        arrays["denoised_first"] = den[0]
+        arrays["denoised_last"] = den[-1]
+    save(name, **arrays)
+
+
+def main():
+    torch.manual_seed(0)
+    gen_attention()
+    gen_blocks()
+    gen_schedules()
+    gen_sampler_kat()
+    gen_cfg()
+    gen_e2e("tiny_sd15", 42, 2, 16, 20, "euler", "normal", 77, 77, "e2e_tiny_sd15_euler")
+    gen_e2e("tiny_sd21v", 43, 2, 12, 25, "euler", "normal", 77, 154, "e2e_tiny_sd21v_euler")
+    gen_e2e("tiny_sdxl", 44, 2, 16, 30, "dpmpp_2m", "karras", 77, 77, "e2e_tiny_sdxl_dpmpp2m")
+    if "--skip-sd15" not in sys.argv:
+        # BASELINE.json configs[0]: SD1.5 512x512 batch 1, 20-step Euler, CFG 7.0, CPU reference path
+        gen_e2e("sd15", 42, 1, 64, 20, "euler", "normal", 77, 77, "e2e_sd15_config1")
+
+
+if __name__ == "__main__":
+    main()

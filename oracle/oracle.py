@@ -229,25 +229,32 @@ def unet_forward(cfg: dict, sd: Dict[str, Tensor], x: Tensor, timesteps: Tensor,
 # ----------------------------------------------------------------------------------------------
 # model sampling   (comfy/model_sampling.py)
 # ----------------------------------------------------------------------------------------------
+def _sigmas_f64(linear_start: float, linear_end: float, n: int) -> Tensor:
+    betas = torch.linspace(linear_start ** 0.5, linear_end ** 0.5, n, dtype=torch.float64) ** 2
+    ac = torch.cumprod(1.0 - betas, dim=0)
+    return ((1 - ac) / ac) ** 0.5
+
+
 def discrete_sigmas(linear_start: float = 0.00085, linear_end: float = 0.012, n: int = 1000) -> Tensor:
     """ModelSamplingDiscrete._register_schedule, 'linear' betas in float64 -> float32 sigmas
     (model_sampling.py:53-76; util.py:89-93)."""
-    betas = torch.linspace(linear_start ** 0.5, linear_end ** 0.5, n, dtype=torch.float64) ** 2
-    ac = torch.cumprod(1.0 - betas, dim=0)
-    return (((1 - ac) / ac) ** 0.5).float()
+    return _sigmas_f64(linear_start, linear_end, n).float()
 
 
-def timestep_of_sigma(sigma: Tensor, sigmas: Tensor) -> Tensor:
+def discrete_log_sigmas(linear_start: float = 0.00085, linear_end: float = 0.012, n: int = 1000) -> Tensor:
+    """set_sigmas: the log table is taken in float64 and then rounded (model_sampling.py:74-76)."""
+    return _sigmas_f64(linear_start, linear_end, n).log().float()
+
+
+def timestep_of_sigma(sigma: Tensor, log_sigmas: Tensor) -> Tensor:
     """ModelSamplingDiscrete.timestep: argmin |log sigma - log sigma_j| (model_sampling.py:86-89)."""
-    log_sigmas = sigmas.log()
     dists = sigma.log() - log_sigmas[:, None]
     return dists.abs().argmin(dim=0).view(sigma.shape)
 
 
-def sigma_of_timestep(t: Tensor, sigmas: Tensor) -> Tensor:
+def sigma_of_timestep(t: Tensor, log_sigmas: Tensor) -> Tensor:
     """ModelSamplingDiscrete.sigma: log-linear interpolation (model_sampling.py:91-97)."""
-    log_sigmas = sigmas.log()
-    t = torch.clamp(t.float(), min=0, max=len(sigmas) - 1)
+    t = torch.clamp(t.float(), min=0, max=len(log_sigmas) - 1)
     lo, hi, w = t.floor().long(), t.ceil().long(), t.frac()
     return ((1 - w) * log_sigmas[lo] + w * log_sigmas[hi]).exp()
 
@@ -285,11 +292,11 @@ def get_sigmas_karras(n: int, sigma_min: float, sigma_max: float, rho: float = 7
     return torch.cat([sigmas, sigmas.new_zeros([1])])
 
 
-def normal_scheduler(sigmas_table: Tensor, steps: int, sgm: bool = False) -> Tensor:
-    start = timestep_of_sigma(sigmas_table[-1], sigmas_table)
-    end = timestep_of_sigma(sigmas_table[0], sigmas_table)
+def normal_scheduler(sigmas_table: Tensor, log_sigmas: Tensor, steps: int, sgm: bool = False) -> Tensor:
+    start = timestep_of_sigma(sigmas_table[-1], log_sigmas)
+    end = timestep_of_sigma(sigmas_table[0], log_sigmas)
     ts = torch.linspace(start, end, steps + 1)[:-1] if sgm else torch.linspace(start, end, steps)
-    sigs = [float(sigma_of_timestep(t, sigmas_table)) for t in ts]
+    sigs = [float(sigma_of_timestep(t, log_sigmas)) for t in ts]
     return torch.FloatTensor(sigs + [0.0])
 
 
@@ -299,13 +306,14 @@ def simple_scheduler(sigmas_table: Tensor, steps: int) -> Tensor:
     return torch.FloatTensor(sigs + [0.0])
 
 
-def calculate_sigmas(sigmas_table: Tensor, scheduler: str, steps: int) -> Tensor:
+def calculate_sigmas(sigmas_table: Tensor, scheduler: str, steps: int, log_sigmas: Optional[Tensor] = None) -> Tensor:
+    log_sigmas = discrete_log_sigmas() if log_sigmas is None else log_sigmas
     if scheduler == 'karras':
         return get_sigmas_karras(steps, float(sigmas_table[0]), float(sigmas_table[-1]))
     if scheduler == 'normal':
-        return normal_scheduler(sigmas_table, steps)
+        return normal_scheduler(sigmas_table, log_sigmas, steps)
     if scheduler == 'sgm_uniform':
-        return normal_scheduler(sigmas_table, steps, sgm=True)
+        return normal_scheduler(sigmas_table, log_sigmas, steps, sgm=True)
     if scheduler == 'simple':
         return simple_scheduler(sigmas_table, steps)
     raise ValueError(scheduler)
@@ -402,7 +410,8 @@ def sample(cfg: dict, sd: Dict[str, Tensor], prediction: str, scale_factor: floa
            callback=None, max_steps: Optional[int] = None) -> Tensor:
     """comfy.sample.sample -> KSampler -> CFGGuider -> KSAMPLER -> sample_<name> with plain conds."""
     table = discrete_sigmas()
-    sigmas = calculate_sigmas(table, scheduler, steps)
+    log_table = discrete_log_sigmas()
+    sigmas = calculate_sigmas(table, scheduler, steps, log_table)
     if max_steps is not None:
         sigmas = sigmas[:max_steps + 1]
     extra_c = extra_u = None
@@ -413,7 +422,7 @@ def sample(cfg: dict, sd: Dict[str, Tensor], prediction: str, scale_factor: floa
 
     def apply_model(x, sigma, context, y=None):
         xc = calculate_input(sigma, x)
-        t = timestep_of_sigma(sigma, table).float()
+        t = timestep_of_sigma(sigma, log_table).float()
         out = unet_forward(cfg, sd, xc, t, context, y)
         return calculate_denoised(sigma, out, x, prediction)
 

@@ -1,0 +1,258 @@
+"""Kernel parity on the GPU: every C-ABI entry point (through the ctypes binding) against the oracle
+on the same seeded inputs and against the reference's golden outputs. Tolerances:
+  attention                    2e-2 max-abs in bf16 (BASELINE.json north_star)
+  LayerNorm / GEGLU / linear   1 bf16 ulp of the output magnitude (inputs are bf16-rounded first)
+  CFG / sampler tail           bit-exact (fp32, reference operation order)
+"""
+import math
+
+import pytest
+import torch
+
+from conftest import load_golden, randn
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+ATTN_TOL = 2e-2
+
+
+def N():
+    from comfy_gen_server_b200 import _native
+    return _native
+
+
+def bf(t):
+    return t.to("cuda", torch.bfloat16)
+
+
+def ulp_tol(ref):
+    return float(ref.abs().max()) * 2 ** -7 + 1e-3
+
+
+# ------------------------------------------------------------------------------------------ attention
+@pytest.mark.parametrize("name", ["self_d64", "cross77_d40", "cross154_d80", "self_d160_ragged"])
+def test_attention_golden(name):
+    g = load_golden("attention")
+    q, k, v, h = g[f"{name}.q"], g[f"{name}.k"], g[f"{name}.v"], int(g[f"{name}.heads"])
+    out = N().attention(bf(q), bf(k), bf(v), h).float().cpu()
+    assert (out - g[f"{name}.out"]).abs().max() < ATTN_TOL          # vs the reference's fp32 output
+    ref = O.attention(bf(q).float().cpu(), bf(k).float().cpu(), bf(v).float().cpu(), h)
+    assert (out - ref).abs().max() < ATTN_TOL / 2                   # vs the oracle on the same bf16 inputs
+
+
+ATTN_SHAPES = [
+    # B, H, Nq, Nk, d          -- the geometries of SURVEY.md section 8 (scaled-down batch)
+    (2, 10, 4096, 4096, 64), (1, 20, 1024, 1024, 64), (2, 10, 4096, 77, 64), (2, 20, 1024, 154, 64),
+    (2, 8, 4096, 4096, 40), (2, 8, 1024, 1024, 80), (2, 8, 256, 256, 160), (2, 8, 64, 64, 160),
+    (2, 8, 64, 77, 160), (1, 5, 9216, 9216, 64), (2, 10, 2304, 2304, 64), (2, 20, 576, 576, 64),
+    (2, 20, 144, 144, 64), (2, 20, 144, 77, 64), (1, 1, 1, 1, 64), (3, 2, 129, 255, 64), (1, 2, 300, 231, 8),
+    (1, 3, 257, 16, 16),
+]
+
+
+@pytest.mark.parametrize("B,H,Nq,Nk,d", ATTN_SHAPES)
+def test_attention_vs_fp32(B, H, Nq, Nk, d):
+    q, k, v = bf(randn((B, Nq, H * d), 1)), bf(randn((B, Nk, H * d), 2)), bf(randn((B, Nk, H * d), 3))
+    out = N().attention(q, k, v, H).float()
+    qf, kf, vf = (t.float().view(B, -1, H, d).transpose(1, 2) for t in (q, k, v))
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * d ** -0.5, -1) @ vf).transpose(1, 2).reshape(B, Nq, H * d)
+    assert not torch.isnan(out).any()
+    assert (out - ref).abs().max() < ATTN_TOL
+
+
+def test_attention_large_logits_rescale_path():
+    B, H, Nq, Nk, d = 1, 2, 384, 2048, 64
+    q, k, v = bf(randn((B, Nq, H * d), 1, 4.0)), bf(randn((B, Nk, H * d), 2, 4.0)), bf(randn((B, Nk, H * d), 3))
+    out = N().attention(q, k, v, H).float()
+    ref = O.attention(q.float().cpu(), k.float().cpu(), v.float().cpu(), H).cuda()
+    assert (out - ref).abs().max() < ATTN_TOL
+
+
+def test_attention_properties_full_size():
+    """Size-independent properties at a BASELINE.json full size (SDXL 1024^2 level 1: 4096 tokens):
+    rows of softmax sum to one (v = const -> out = const); permuting the keys does not change the result."""
+    B, H, Nn, d = 2, 10, 4096, 64
+    q, k = bf(randn((B, Nn, H * d), 1)), bf(randn((B, Nn, H * d), 2))
+    ones = torch.full((B, Nn, H * d), 0.5, device="cuda", dtype=torch.bfloat16)
+    out = N().attention(q, k, ones, H).float()
+    assert (out - 0.5).abs().max() < 4e-3
+    v = bf(randn((B, Nn, H * d), 3))
+    perm = torch.randperm(Nn, generator=torch.Generator().manual_seed(0)).cuda()
+    a = N().attention(q, k, v, H).float()
+    b = N().attention(q, k[:, perm].contiguous(), v[:, perm].contiguous(), H).float()
+    assert (a - b).abs().max() < 8e-3
+
+
+def test_attention_strided_views_of_fused_qkv():
+    B, Nn, H, d = 2, 512, 4, 64
+    qkv = bf(randn((B, Nn, 3 * H * d), 5))
+    q, k, v = qkv[..., :H * d], qkv[..., H * d:2 * H * d], qkv[..., 2 * H * d:]
+    a = N().attention(q, k, v, H)
+    b = N().attention(q.contiguous(), k.contiguous(), v.contiguous(), H)
+    assert torch.equal(a, b)
+    assert torch.equal(qkv, bf(randn((B, Nn, 3 * H * d), 5)))      # inputs untouched
+
+
+def test_attention_errors_and_empty():
+    n = N()
+    q = bf(randn((1, 16, 64), 1))
+    with pytest.raises(RuntimeError):
+        n.attention(q.cpu(), q.cpu(), q.cpu(), 1)                  # no CPU fallback
+    with pytest.raises(RuntimeError):
+        n.attention(q.float(), q.float(), q.float(), 1)            # bf16 only
+    with pytest.raises(RuntimeError):
+        n.attention(bf(randn((1, 16, 12), 1)), bf(randn((1, 16, 12), 1)), bf(randn((1, 16, 12), 1)), 1)  # d % 8
+    with pytest.raises(RuntimeError):
+        n.attention(q, q[:, :0], q[:, :0], 1)                      # empty key set
+    assert n.attention(q[:, :0], q, q, 1).shape == (1, 0, 64)
+
+
+# ------------------------------------------------------------------------------------------ LayerNorm
+@pytest.mark.parametrize("rows,C", [(64, 128), (2 * 4096, 320), (2 * 1024, 640), (2 * 1024, 1280), (7, 2560), (1, 8)])
+def test_layernorm_vs_oracle(rows, C):
+    x, w, b = bf(randn((rows, C), 1, 2.0)), bf(randn((C,), 2) * 0.2 + 1), bf(randn((C,), 3) * 0.2)
+    y = N().layer_norm(x, w, b, 1e-5).float().cpu()
+    ref = O.layer_norm(x.float().cpu(), w.float().cpu(), b.float().cpu())
+    assert (y - ref).abs().max() <= ulp_tol(ref)
+
+
+def test_layernorm_golden_and_fused_residual():
+    g = load_golden("blocks")
+    from comfy_gen_server_b200 import unet_config as uc
+    dim = int(g["dim"])
+    sd = uc.seeded_state_dict({"weight": (dim,), "bias": (dim,)}, 100)
+    y = N().layer_norm(bf(g["x"]), bf(sd["weight"]), bf(sd["bias"]), 1e-5).float().cpu()
+    assert (y - g["layernorm.out"]).abs().max() < 3e-2
+    x, r = bf(randn((300, 640), 1)), bf(randn((300, 640), 2))
+    w, b = bf(sd["weight"].repeat(5)), bf(sd["bias"].repeat(5))
+    xs = x.clone()
+    y2 = N().add_layer_norm_(xs, r, w, b, 1e-5)
+    assert torch.equal(xs, x + r)                                  # bf16 in-place residual, as the reference
+    assert torch.equal(y2, N().layer_norm(x + r, w, b, 1e-5))
+
+
+def test_layernorm_errors_and_empty():
+    n = N()
+    w = bf(torch.ones(12))
+    with pytest.raises(RuntimeError):
+        n.layer_norm(bf(torch.ones(4, 12)), w, w)                  # C % 8 != 0
+    with pytest.raises(RuntimeError):
+        n.layer_norm(torch.ones(4, 16), w, w)                      # CPU tensor
+    assert n.layer_norm(bf(torch.ones(0, 16)), bf(torch.ones(16)), bf(torch.ones(16))).shape == (0, 16)
+
+
+# ------------------------------------------------------------------------------------------ GEMMs
+@pytest.mark.parametrize("M,K,Nn", [(128, 64, 128), (300, 320, 1280), (2 * 1024, 640, 2560), (2 * 256, 1280, 5120),
+                                    (1, 128, 128), (4096 + 17, 320, 1280)])
+def test_geglu_vs_oracle(M, K, Nn):
+    x, w, b = bf(randn((M, K), 1)), bf(randn((2 * Nn, K), 2, K ** -0.5)), bf(randn((2 * Nn,), 3, 0.1))
+    y = N().geglu(x, w, b).float().cpu()
+    ref = O.geglu(x.float().cpu(), w.float().cpu(), b.float().cpu())
+    assert (y - ref).abs().max() <= ulp_tol(ref)
+
+
+def test_geglu_golden():
+    g = load_golden("blocks")
+    from comfy_gen_server_b200 import unet_config as uc
+    dim = int(g["dim"])
+    sd = uc.seeded_state_dict({"proj.weight": (dim * 8, dim), "proj.bias": (dim * 8,)}, 101)
+    y = N().geglu(bf(g["x"]), bf(sd["proj.weight"]), bf(sd["proj.bias"])).float().cpu()
+    assert (y - g["geglu.out"]).abs().max() < 3e-2
+
+
+@pytest.mark.parametrize("M,K,Nn,res", [(128, 64, 256, False), (256, 320, 320, True), (1000, 1280, 640, True),
+                                        (2 * 1024, 5120, 1280, False), (77, 2048, 1280, False)])
+def test_linear_vs_oracle(M, K, Nn, res):
+    x, w, b = bf(randn((M, K), 1)), bf(randn((Nn, K), 2, K ** -0.5)), bf(randn((Nn,), 3, 0.1))
+    r = bf(randn((M, Nn), 4)) if res else None
+    y = N().linear(x, w, b, r).float().cpu()
+    ref = O.linear(x.float().cpu(), w.float().cpu(), b.float().cpu())
+    if res:
+        ref = ref + r.float().cpu()
+    assert (y - ref).abs().max() <= ulp_tol(ref)
+
+
+def test_gemm_errors():
+    n = N()
+    with pytest.raises(RuntimeError):
+        n.geglu(bf(randn((8, 64), 1)), bf(randn((2 * 100, 64), 2)), None)     # N % 128
+    with pytest.raises(RuntimeError):
+        n.geglu(randn((8, 64), 1), randn((256, 64), 2), None)                 # CPU tensors
+
+
+# ------------------------------------------------------------------------------------------ CFG / sampler tail
+@pytest.mark.parametrize("pred", ["eps", "v"])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_cfg_denoise_bit_exact(pred, out_dtype):
+    B = 3
+    x = randn((B, 4, 24, 24), 1, 5.0)
+    eu, ec = randn((B, 4, 24, 24), 2).to(out_dtype), randn((B, 4, 24, 24), 3).to(out_dtype)
+    sig = torch.tensor([14.6146, 2.5, 0.0292])
+    d = N().cfg_denoise(x.cuda(), eu.cuda(), ec.cuda(), sig.cuda(), 7.0, 0 if pred == "eps" else 1).cpu()
+    dc = O.calculate_denoised(sig, ec.float(), x, pred)
+    du = O.calculate_denoised(sig, eu.float(), x, pred)
+    assert torch.equal(d, O.cfg_function(dc, du, 7.0))
+    d1 = N().cfg_denoise(x.cuda(), None, ec.cuda(), sig.cuda(), 1.0, 0 if pred == "eps" else 1).cpu()
+    assert torch.equal(d1, dc)
+
+
+def test_unet_input_matches_reference_formula():
+    g = load_golden("schedules")
+    xi = N().unet_input(g["ci.x"].cuda(), g["ci.sigma"].cuda(), 2).float().cpu()
+    ref = g["calculate_input"].to(torch.bfloat16).float()
+    assert torch.equal(xi[:2], ref) and torch.equal(xi[2:], ref)
+
+
+@pytest.mark.parametrize("key", ["euler_normal_20", "dpmpp_2m_karras_30", "euler_karras_7", "dpmpp_2m_normal_25"])
+def test_sampler_known_answer_bit_exact_on_gpu(key):
+    """The reference's sampler loops with a Gaussian denoiser, driven through the product's sampler functions and
+    the CUDA update kernels: final x bit-identical to the reference's (golden)."""
+    from comfy_gen_server_b200.k_diffusion import sampling as ks
+    g = load_golden("sampler_kat")
+    fn = ks.sample_dpmpp_2m if key.startswith("dpmpp") else ks.sample_euler
+    # the denoiser is evaluated with torch on the host copy so that only the update kernels are under test
+    model = lambda x, sigma, **kw: (x.cpu() / (1.0 + sigma.cpu().view(-1, 1, 1, 1) ** 2)).cuda()
+    trace = []
+    xf = fn(model, g[key + ".x0"].cuda(), g[key + ".sigmas"].cuda(), extra_args={},
+            callback=lambda d: trace.append(d["denoised"]))
+    assert torch.equal(xf.cpu(), g[key + ".final"])
+    assert torch.equal(trace[-1].cpu(), g[key + ".denoised_last"])
+    const = fn(lambda x, s, **kw: torch.full_like(x, 0.25), g[key + ".x0"].cuda(), g[key + ".sigmas"].cuda())
+    assert (const - 0.25).abs().max() == 0.0
+
+
+@pytest.mark.parametrize("mode", [1, 2, 3])
+def test_fused_tail_equals_separate_kernels(mode):
+    n = N()
+    B = 2
+    x = randn((B, 4, 32, 32), 1, 3.0).cuda()
+    eu, ec = bf(randn((B, 4, 32, 32), 2)), bf(randn((B, 4, 32, 32), 3))
+    dold = randn((B, 4, 32, 32), 4).cuda()
+    sig = torch.full((B,), 2.5).cuda()
+    c = (2.5, -0.7, 0.0, 0.0) if mode == 1 else (0.8, -0.3, 1.4, 0.4)
+    d, xn = n.cfg_sampler_tail(x, eu, ec, sig, 7.0, 0, dold if mode == 3 else None, mode, *c)
+    d_ref = n.cfg_denoise(x, eu, ec, sig, 7.0, 0)
+    if mode == 1:
+        x_ref = n.sampler_step_euler(x, d_ref, c[0], c[1])
+    else:
+        x_ref = n.sampler_step_dpmpp2m(x, d_ref, dold if mode == 3 else None, *c)
+    assert torch.equal(d, d_ref) and torch.equal(xn, x_ref)
+
+
+def test_tail_large_and_ragged_sizes():
+    """2048^2 latents (config 5) and a batch that does not fill a whole block."""
+    n = N()
+    for B, hw in [(4, 256), (1, 2)]:
+        x = randn((B, 4, hw, hw), 1).cuda()
+        d = randn((B, 4, hw, hw), 2).cuda()
+        xe = n.sampler_step_euler(x, d, 3.0, -1.0).cpu()
+        assert torch.equal(xe, x.cpu() + (x.cpu() - d.cpu()) / torch.tensor(3.0) * torch.tensor(-1.0))
+
+
+def test_tail_errors():
+    n = N()
+    x = randn((1, 3, 5, 5), 1).cuda()       # 75 elements per sample: not a multiple of 4
+    with pytest.raises(RuntimeError):
+        n.cfg_denoise(x, None, x, torch.ones(1).cuda(), 1.0, 0)
+    with pytest.raises(RuntimeError):
+        n.sampler_step_euler(randn((1, 4, 4, 4), 1), randn((1, 4, 4, 4), 1), 1.0, 1.0)      # CPU tensors
