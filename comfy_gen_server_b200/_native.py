@@ -73,6 +73,55 @@ def load_library(path: Optional[str] = None) -> ctypes.CDLL:
         return lib
 
 
+# Launch accounting for bench.py: every successful C-ABI launch is counted by kernel family, and a family
+# can be bracketed with CUDA events (on the launching stream) to time it inside a larger step.
+LAUNCHES: dict = {}
+_timed_family: Optional[str] = None
+_timed_events: list = []
+_timed_work: list = []
+
+
+def reset_launch_counters() -> None:
+    LAUNCHES.clear()
+    _timed_events.clear()
+    _timed_work.clear()
+
+
+def time_family(name: Optional[str]) -> None:
+    """Bracket every launch of kernel family `name` with CUDA events (None switches it off)."""
+    global _timed_family
+    _timed_family = name
+
+
+def timed_family_totals():
+    """(total ms, total algorithmic work units, launches) of the timed family since the last reset.
+    Call after a device synchronize."""
+    ms = sum(a.elapsed_time(b) for a, b in _timed_events)
+    return ms, float(sum(_timed_work)), len(_timed_events)
+
+
+class _Launch:
+    """with _Launch('attention', stream_tensor, work): rc = lib.fn(...)"""
+    __slots__ = ("family", "t", "work", "ev")
+
+    def __init__(self, family, t, work=0.0):
+        self.family, self.t, self.work, self.ev = family, t, work, None
+
+    def __enter__(self):
+        LAUNCHES[self.family] = LAUNCHES.get(self.family, 0) + 1
+        if _timed_family == self.family:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record(torch.cuda.current_stream(self.t.device))
+        return self
+
+    def __exit__(self, *exc):
+        if self.ev is not None:
+            self.ev[1].record(torch.cuda.current_stream(self.t.device))
+            _timed_events.append(self.ev)
+            _timed_work.append(self.work)
+        return False
+
+
 def _check(rc: int, what: str) -> None:
     if rc != 0:
         msg = load_library().cgs_last_error().decode("utf-8", "replace")
@@ -113,10 +162,11 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> 
     out = torch.empty((B, Nq, inner), dtype=torch.bfloat16, device=q.device)
     if B == 0 or Nq == 0:
         return out
-    rc = load_library().cgs_attention_fwd(
-        q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, heads, Nq, Nk, d,
-        q.stride(0), q.stride(1), d, k.stride(0), k.stride(1), d, v.stride(0), v.stride(1), d,
-        out.stride(0), out.stride(1), d, float(d) ** -0.5, _stream(q))
+    with _Launch("attention", q, 4.0 * B * heads * Nq * Nk * d):
+        rc = load_library().cgs_attention_fwd(
+            q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, heads, Nq, Nk, d,
+            q.stride(0), q.stride(1), d, k.stride(0), k.stride(1), d, v.stride(0), v.stride(1), d,
+            out.stride(0), out.stride(1), d, float(d) ** -0.5, _stream(q))
     _check(rc, "cgs_attention_fwd")
     return out
 
@@ -132,8 +182,9 @@ def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: f
     xc = x if x.is_contiguous() else x.contiguous()
     y = torch.empty_like(xc)
     rows = xc.numel() // C if C else 0
-    rc = load_library().cgs_layernorm_fwd(xc.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
-                                          rows, C, eps, _stream(x))
+    with _Launch("layernorm", x, 4.0 * rows * C):
+        rc = load_library().cgs_layernorm_fwd(xc.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+                                              rows, C, eps, _stream(x))
     _check(rc, "cgs_layernorm_fwd")
     return y
 
@@ -148,9 +199,10 @@ def add_layer_norm_(x: torch.Tensor, residual: torch.Tensor, weight: torch.Tenso
     C = x.shape[-1]
     y = torch.empty_like(x)
     rows = x.numel() // C if C else 0
-    rc = load_library().cgs_add_layernorm_fwd(x.data_ptr(), residual.data_ptr(), weight.data_ptr(),
-                                              bias.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, eps,
-                                              _stream(x))
+    with _Launch("add_layernorm", x, 10.0 * rows * C):
+        rc = load_library().cgs_add_layernorm_fwd(x.data_ptr(), residual.data_ptr(), weight.data_ptr(),
+                                                  bias.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, eps,
+                                                  _stream(x))
     _check(rc, "cgs_add_layernorm_fwd")
     return y
 
@@ -179,9 +231,10 @@ def geglu(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -
     x2 = _as_2d(x)
     M = x2.shape[0]
     y = torch.empty((*x.shape[:-1], N), dtype=torch.bfloat16, device=x.device)
-    rc = load_library().cgs_geglu_gemm_fwd(x2.data_ptr(), weight.data_ptr(),
-                                           bias.data_ptr() if bias is not None else None, y.data_ptr(),
-                                           M, N, K, x2.stride(0), weight.stride(0), N, _stream(x))
+    with _Launch("geglu_gemm", x, 4.0 * M * K * N):
+        rc = load_library().cgs_geglu_gemm_fwd(x2.data_ptr(), weight.data_ptr(),
+                                               bias.data_ptr() if bias is not None else None, y.data_ptr(),
+                                               M, N, K, x2.stride(0), weight.stride(0), N, _stream(x))
     _check(rc, "cgs_geglu_gemm_fwd")
     return y
 
@@ -209,10 +262,11 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
         r_ptr = residual.data_ptr()
     if bias is not None:
         _require_cuda("linear bias", bias, torch.bfloat16)
-    rc = load_library().cgs_linear_fwd(x2.data_ptr(), weight.data_ptr(),
-                                       bias.data_ptr() if bias is not None else None, r_ptr,
-                                       out.data_ptr(), M, N, K, x2.stride(0), weight.stride(0), N, N,
-                                       _stream(x))
+    with _Launch("linear", x, 2.0 * M * K * N):
+        rc = load_library().cgs_linear_fwd(x2.data_ptr(), weight.data_ptr(),
+                                           bias.data_ptr() if bias is not None else None, r_ptr,
+                                           out.data_ptr(), M, N, K, x2.stride(0), weight.stride(0), N, N,
+                                           _stream(x))
     _check(rc, "cgs_linear_fwd")
     return out
 
@@ -233,8 +287,9 @@ def unet_input(x: torch.Tensor, sigma: torch.Tensor, copies: int, sigma_data: fl
     B = x.shape[0]
     per = x.numel() // B if B else 0
     out = torch.empty((copies * B, *x.shape[1:]), dtype=torch.bfloat16, device=x.device)
-    rc = load_library().cgs_unet_input_fwd(x.data_ptr(), sigma.data_ptr(), out.data_ptr(), B, per, copies,
-                                           sigma_data, _stream(x))
+    with _Launch("unet_input", x, float(x.numel()) * (4 + 2 * copies)):
+        rc = load_library().cgs_unet_input_fwd(x.data_ptr(), sigma.data_ptr(), out.data_ptr(), B, per, copies,
+                                               sigma_data, _stream(x))
     _check(rc, "cgs_unet_input_fwd")
     return out
 
@@ -261,9 +316,10 @@ def cfg_denoise(x, model_out_uncond, model_out_cond, sigma, cond_scale: float, p
     B = x.shape[0]
     per = x.numel() // B if B else 0
     out = torch.empty_like(x)
-    rc = load_library().cgs_cfg_denoise_fwd(x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(),
-                                            cond_scale, pred_type, sigma_data, out.data_ptr(), B, per,
-                                            _stream(x))
+    with _Launch("cfg_denoise", x):
+        rc = load_library().cgs_cfg_denoise_fwd(x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(),
+                                                cond_scale, pred_type, sigma_data, out.data_ptr(), B, per,
+                                                _stream(x))
     _check(rc, "cgs_cfg_denoise_fwd")
     return out
 
@@ -272,8 +328,9 @@ def sampler_step_euler(x, denoised, sigma_hat: float, dt: float, out: Optional[t
     _flat_f32("euler x", x)
     _flat_f32("euler denoised", denoised)
     out = torch.empty_like(x) if out is None else out
-    rc = load_library().cgs_sampler_step_euler(x.data_ptr(), denoised.data_ptr(), sigma_hat, dt,
-                                               out.data_ptr(), x.numel(), _stream(x))
+    with _Launch("sampler_step", x):
+        rc = load_library().cgs_sampler_step_euler(x.data_ptr(), denoised.data_ptr(), sigma_hat, dt,
+                                                   out.data_ptr(), x.numel(), _stream(x))
     _check(rc, "cgs_sampler_step_euler")
     return out
 
@@ -285,9 +342,10 @@ def sampler_step_dpmpp2m(x, denoised, old_denoised, c_x: float, c_d: float, c_cu
     if old_denoised is not None:
         _flat_f32("dpmpp2m old_denoised", old_denoised)
     out = torch.empty_like(x) if out is None else out
-    rc = load_library().cgs_sampler_step_dpmpp2m(
-        x.data_ptr(), denoised.data_ptr(), old_denoised.data_ptr() if old_denoised is not None else None,
-        c_x, c_d, c_cur, c_old, out.data_ptr(), x.numel(), _stream(x))
+    with _Launch("sampler_step", x):
+        rc = load_library().cgs_sampler_step_dpmpp2m(
+            x.data_ptr(), denoised.data_ptr(), old_denoised.data_ptr() if old_denoised is not None else None,
+            c_x, c_d, c_cur, c_old, out.data_ptr(), x.numel(), _stream(x))
     _check(rc, "cgs_sampler_step_dpmpp2m")
     return out
 
@@ -305,10 +363,11 @@ def cfg_sampler_tail(x, model_out_uncond, model_out_cond, sigma, cond_scale: flo
     per = x.numel() // B if B else 0
     denoised = torch.empty_like(x)
     x_next = torch.empty_like(x) if x_out is None else x_out
-    rc = load_library().cgs_cfg_sampler_tail_fwd(
-        x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(), cond_scale, pred_type, sigma_data,
-        old_denoised.data_ptr() if old_denoised is not None else None, sampler, c0, c1, c2, c3,
-        denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
+    with _Launch("cfg_sampler_tail", x, float(x.numel()) * (16 + 4 * (2 if is_bf16 else 4) // 2)):
+        rc = load_library().cgs_cfg_sampler_tail_fwd(
+            x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(), cond_scale, pred_type, sigma_data,
+            old_denoised.data_ptr() if old_denoised is not None else None, sampler, c0, c1, c2, c3,
+            denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
     _check(rc, "cgs_cfg_sampler_tail_fwd")
     return denoised, x_next
 

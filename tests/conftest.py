@@ -40,5 +40,5 @@ def randn(shape, seed, scale=1.0):
 
 
 def cosine(a, b):
-    a, b = a.double().flatten(), b.double().flatten()
+    a, b = a.detach().double().flatten(), b.detach().double().flatten()
     return float((a @ b) / (a.norm() * b.norm()))

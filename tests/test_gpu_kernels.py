@@ -157,7 +157,8 @@ def test_geglu_golden():
     dim = int(g["dim"])
     sd = uc.seeded_state_dict({"proj.weight": (dim * 8, dim), "proj.bias": (dim * 8,)}, 101)
     y = N().geglu(bf(g["x"]), bf(sd["proj.weight"]), bf(sd["proj.bias"])).float().cpu()
-    assert (y - g["geglu.out"]).abs().max() < 3e-2
+    # vs the reference's fp32 output on fp32 inputs: bf16 rounding of x, W and y (1 ulp each of |y|max ~ 8)
+    assert (y - g["geglu.out"]).abs().max() <= 2 * ulp_tol(g["geglu.out"])
 
 
 @pytest.mark.parametrize("M,K,Nn,res", [(128, 64, 256, False), (256, 320, 320, True), (1000, 1280, 640, True),
