@@ -8,10 +8,18 @@
 // The same kernel (EPI_LINEAR) serves plain Linear layers  y = x W^T (+ b) (+ residual)
 // (reference comfy/ops.py:40-52), used for to_q/to_k/to_v/to_out/ff.net.2/proj_in/proj_out.
 //
-// Structure (one persistent CTA per SM, 192 threads):
-//   warp 0      TMA producer: A tile [128 x 64] and B tile [256 x 64] per k-block, 4-stage ring
-//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=256, K=16 x 4 per block)
-//   warps 2..5  epilogue: tcgen05.ld accumulator -> bias/GELU/gate -> bf16 -> global
+// Structure (one persistent CTA per SM, 576 threads):
+//   warp 0       TMA producer: A tile [128 x 64] and B tile [256 x 64] per k-block, 4-stage ring
+//   warp 1       TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=256, K=16 x 4 per block)
+//   warps 2..17  epilogue (4 warps per TMEM lane quadrant, each owning a 32/64-column slice):
+//                tcgen05.ld accumulator -> bias/GELU/gate -> bf16 -> global.
+// 16 epilogue warps, not 4: the first version (4 warps, erff) ran one warp per scheduler at IPC 0.24 and
+// needed 23.8 k cycles per tile against 5.1 k cycles of MMA (ncu, profiles/r01_*): latency-bound. Four
+// warps per scheduler hide the TMEM-load / MUFU / store latencies, and a branch-free erf halves the
+// instruction count. Tiles are walked in groups of 8 M-blocks x all N-blocks so the A panel of a group
+// stays in L2 while its N-blocks are produced (the M-fastest order re-read A from DRAM 9x).
+// Output goes registers -> 128-byte-swizzled SMEM staging tile -> TMA store: with direct row-strided
+// 16-byte global stores the kernel was store-bound (872 TFLOP/s; 1645 with the stores removed).
 // Accumulators are double-buffered in TMEM (2 x 256 fp32 columns = all 512 columns), so the
 // epilogue of tile i overlaps the MMAs of tile i+1.
 //
@@ -21,6 +29,8 @@
 //
 // Tensor-core bound. Algorithmic FLOPs = 2 * M * K * (2N) for GEGLU, 2 * M * K * N for linear.
 #include "common.cuh"
+
+#include <stdlib.h>
 
 namespace cgs {
 
@@ -33,13 +43,39 @@ constexpr int STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;          // 16 KiB
 constexpr int B_BYTES = UMMA_N * BK * 2;      // 32 KiB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;  // + barriers + alignment slack
-constexpr int THREADS = 192;
+constexpr int OUT_BOX_BYTES = BM * 128;                  // [128 rows x 64 bf16], 128-byte swizzle
+constexpr int OUT_STAGE_BYTES = 2 * OUT_BOX_BYTES;       // 128 output columns per pass
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGE_BYTES + 256 + 1024;  // + barriers + slack
+constexpr int EPI_WARPS = 16;
+constexpr int THREADS = (2 + EPI_WARPS) * 32;
+constexpr int GROUP_M = 8;
 enum { EPI_LINEAR = 0, EPI_GEGLU = 1 };
 }  // namespace gemm
 
+// Exact-erf GELU, 0.5 x (1 + erf(x / sqrt 2)), with erf from Abramowitz & Stegun 7.1.26
+// (|error| <= 1.5e-7, far below bf16 resolution), branch-free: 1 MUFU.RCP + 1 MUFU.EX2 + ~10 FMA-pipe ops.
 __device__ __forceinline__ float gelu_erf(float x) {
-    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+    const float z = fabsf(x) * 0.70710678118654752440f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));   // MUFU.RCP, denominator in [1, inf)
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    p *= t;
+    const float e = ex2_approx(-1.4426950408889634f * z * z);
+    const float erf_abs = fmaf(-p, e, 1.0f);                 // erf(|x| / sqrt 2)
+    const float half_erf = copysignf(0.5f * erf_abs, x);
+    return x * (0.5f + half_erf);
+}
+
+// tile index -> (m block, n block): groups of GROUP_M M-blocks, N-major inside a group
+__device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& mb, int& nb) {
+    const int per_group = gemm::GROUP_M * tiles_n;
+    const int g = t / per_group;
+    const int r = t - g * per_group;
+    const int gm = min(gemm::GROUP_M, tiles_m - g * gemm::GROUP_M);
+    nb = r / gm;
+    mb = g * gemm::GROUP_M + (r - nb * gm);
 }
 
 struct alignas(16) BF8 {
@@ -49,13 +85,14 @@ struct alignas(16) BF8 {
 template <int EPI>
 __global__ void __launch_bounds__(gemm::THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
-            __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr) {
+            const __grid_constant__ CUtensorMap tmO, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
+            __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr, int dbg) {
     using namespace gemm;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint8_t* out_stage = smem + STAGES * STAGE_BYTES;
+    uint64_t* full = reinterpret_cast<uint64_t*>(out_stage + OUT_STAGE_BYTES);
     uint64_t* empty = full + STAGES;
     uint64_t* tfull = empty + STAGES;
     uint64_t* tempty = tfull + 2;
@@ -71,6 +108,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (warp == 0 && elect_one()) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmO);
     }
     if (warp == 1) {
         if (elect_one()) {
@@ -80,7 +118,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             for (int i = 0; i < 2; ++i) {
                 mbar_init(&tfull[i], 1);
-                mbar_init(&tempty[i], 128);
+                mbar_init(&tempty[i], EPI_WARPS);
             }
             fence_mbar_init();
         }
@@ -99,8 +137,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t % tiles_m) * BM;
-                const int nb = t / tiles_m;
+                int mb, nb;
+                tile_coords(t, tiles_m, tiles_n, mb, nb);
+                const int m0 = mb * BM;
                 const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N;
                 const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : nb * UMMA_N + BN_HALF;
                 for (int kb = 0; kb < kblocks; ++kb) {
@@ -109,8 +148,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     uint8_t* sb = sa + A_BYTES;
                     mbar_expect_tx(&full[stage], STAGE_BYTES);
                     tma_load_2d(sa, &tmA, &full[stage], kb * BK, m0);
-                    tma_load_2d(sb, &tmB, &full[stage], kb * BK, row0);
-                    tma_load_2d(sb + BN_HALF * BK * 2, &tmB, &full[stage], kb * BK, row1);
+                    if (dbg & 4) {   // experiment: reload the A box instead of B (1/3 of the distinct L2 lines)
+                        tma_load_2d(sb, &tmA, &full[stage], kb * BK, m0);
+                        tma_load_2d(sb + BN_HALF * BK * 2, &tmA, &full[stage], kb * BK, m0);
+                    } else {
+                        tma_load_2d(sb, &tmB, &full[stage], kb * BK, row0);
+                        tma_load_2d(sb + BN_HALF * BK * 2, &tmB, &full[stage], kb * BK, row1);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -137,7 +181,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
                         // +32 bytes per k-step inside the 128-byte swizzle row (>> 4 == 2)
-                        umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        if (!(dbg & 8) || k == 0)
+                            umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                     }
                     tc_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -149,27 +194,39 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         __syncwarp();
     } else {
         // ------------------------------ epilogue ----------------------------------
-        const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+        const int quad = warp & 3;               // TMEM lane quadrant this warp may access
+        const int cg = (warp - 2) >> 2;          // 32-column group 0..3 of a 128-column pass
         const int row_in_tile = quad * 32 + lane;
+        const bool store_leader = (warp == 2 && lane == 0);
+        constexpr int EPI_THREADS = EPI_WARPS * 32;
+        // this thread's 64 bytes of the staging tile: box = cg / 2, 16-byte chunks ((cg & 1) * 4 + j) ^ (row & 7)
+        uint8_t* my_stage = out_stage + (cg >> 1) * OUT_BOX_BYTES + row_in_tile * 128;
+        const int chunk0 = (cg & 1) * 4;
+        const int sw = row_in_tile & 7;
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const int m0 = (t % tiles_m) * BM;
-            const int nb = t / tiles_m;
-            const int row = m0 + row_in_tile;
+            int mb, nb;
+            tile_coords(t, tiles_m, tiles_n, mb, nb);
+            const int row = mb * BM + row_in_tile;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * UMMA_N + (static_cast<uint32_t>(quad * 32) << 16);
-            if (EPI == EPI_GEGLU) {
-                const int n0 = nb * BN_HALF;
+            constexpr int PASSES = (EPI == EPI_GEGLU) ? 1 : 2;
 #pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
+            for (int pass = 0; pass < PASSES; ++pass) {
+                BF8 o[4];
+                int col;
+                if (EPI == EPI_GEGLU) {
+                    col = nb * BN_HALF + cg * 32;
                     uint32_t v[32], g[32];
-                    tmem_ld_x32(taddr + c * 32, v);
-                    tmem_ld_x32(taddr + BN_HALF + c * 32, g);
+                    tmem_ld_x32(taddr + cg * 32, v);
+                    tmem_ld_x32(taddr + BN_HALF + cg * 32, g);
                     tmem_wait_ld();
-                    const int col = n0 + c * 32;
-                    BF8 o[4];
+                    // accumulator is in registers: hand the TMEM buffer back to the MMA warp now
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty[acc]);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         BF8 bv, bg;
@@ -189,58 +246,62 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                 fv.x += b0.x; fv.y += b0.y;
                                 fg.x += b1.x; fg.y += b1.y;
                             }
-                            o[q].v[j] = __floats2bfloat162_rn(fv.x * gelu_erf(fg.x),
-                                                              fv.y * gelu_erf(fg.y));
+                            o[q].v[j] = (dbg & 1) ? __floats2bfloat162_rn(fv.x * fg.x, fv.y * fg.y)
+                                                  : __floats2bfloat162_rn(fv.x * gelu_erf(fg.x), fv.y * gelu_erf(fg.y));
                         }
                     }
-                    if (row < M) {
-                        BF8* dst = reinterpret_cast<BF8*>(out + (size_t)row * ldo + col);
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) dst[q] = o[q];
-                    }
-                }
-            } else {
-                const int n0 = nb * UMMA_N;
-#pragma unroll 1
-                for (int c = 0; c < 8; ++c) {
-                    const int col = n0 + c * 32;
-                    if (col >= N) break;  // warp-uniform
+                } else {
+                    col = nb * UMMA_N + pass * 128 + cg * 32;
                     uint32_t v[32];
-                    tmem_ld_x32(taddr + c * 32, v);
+                    tmem_ld_x32(taddr + pass * 128 + cg * 32, v);
                     tmem_wait_ld();
-                    BF8 o[4];
+                    if (pass == PASSES - 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&tempty[acc]);
+                    }
+                    const bool col_ok = col < N;      // N % 32 == 0: a 32-column group is all in or all out
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         BF8 bv, rv;
-                        if (bias != nullptr) bv = *reinterpret_cast<const BF8*>(bias + col + q * 8);
-                        if (residual != nullptr && row < M)
-                            rv = *reinterpret_cast<const BF8*>(residual + (size_t)row * ldr + col + q * 8);
+                        const bool use_b = bias != nullptr && col_ok;
+                        const bool use_r = residual != nullptr && col_ok && row < M;
+                        if (use_b) bv = *reinterpret_cast<const BF8*>(bias + col + q * 8);
+                        if (use_r) rv = *reinterpret_cast<const BF8*>(residual + (size_t)row * ldr + col + q * 8);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             float2 fv = make_float2(__uint_as_float(v[q * 8 + 2 * j]),
                                                     __uint_as_float(v[q * 8 + 2 * j + 1]));
-                            if (bias != nullptr) {
+                            if (use_b) {
                                 const float2 b0 = __bfloat1622float2(bv.v[j]);
                                 fv.x += b0.x; fv.y += b0.y;
                             }
-                            if (residual != nullptr && row < M) {
+                            if (use_r) {
                                 const float2 r0 = __bfloat1622float2(rv.v[j]);
                                 fv.x += r0.x; fv.y += r0.y;
                             }
                             o[q].v[j] = __floats2bfloat162_rn(fv.x, fv.y);
                         }
                     }
-                    if (row < M) {
-                        BF8* dst = reinterpret_cast<BF8*>(out + (size_t)row * ldo + col);
+                }
+                // staging tile must no longer be read by the previous TMA store
+                if (store_leader) tma_store_wait_read();
+                named_bar_sync(1, EPI_THREADS);
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) dst[q] = o[q];
-                    }
+                for (int q = 0; q < 4; ++q)
+                    *reinterpret_cast<BF8*>(my_stage + (((chunk0 + q) ^ sw) << 4)) = o[q];
+                fence_proxy_async_smem();
+                named_bar_sync(1, EPI_THREADS);
+                if (store_leader && !(dbg & 2)) {
+                    const int c0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N + pass * 128;
+                    if (c0 < N) tma_store_2d(&tmO, out_stage, c0, mb * BM);
+                    if (c0 + 64 < N) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, mb * BM);
+                    tma_store_commit();
                 }
             }
-            tc_fence_before();
-            mbar_arrive(&tempty[acc]);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (store_leader) tma_store_wait_all();
     }
 
     tc_fence_before();
@@ -296,6 +357,16 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
         int rc = make_tmap_bf16(&tmB, w, 2, dims, strides, box);
         if (rc != kOk) return rc;
     }
+    CUtensorMap tmO;
+    {
+        const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+        const uint64_t strides[1] = {(uint64_t)ldo * 2};
+        const uint32_t box[2] = {64, BM};
+        int rc = make_tmap_bf16(&tmO, out, 2, dims, strides, box);
+        if (rc != kOk) return rc;
+    }
+    const char* dbg_env = getenv("CGS_GEMM_DEBUG");
+    const int dbg = dbg_env ? atoi(dbg_env) : 0;
     const int tiles_m = (int)((M + BM - 1) / BM);
     const int tiles_n = (epi == EPI_GEGLU) ? N / BN_HALF : (N + UMMA_N - 1) / UMMA_N;
     const long long tiles = (long long)tiles_m * tiles_n;
@@ -306,13 +377,13 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
     if (epi == EPI_GEGLU) {
         CGS_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<EPI_GEGLU>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        gemm_kernel<EPI_GEGLU><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, bp, rp, op, (int)M, N, K,
-                                                                      (int)ldo, (int)ldr);
+        gemm_kernel<EPI_GEGLU><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K,
+                                                                      (int)ldo, (int)ldr, dbg);
     } else {
         CGS_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<EPI_LINEAR>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        gemm_kernel<EPI_LINEAR><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, bp, rp, op, (int)M, N, K,
-                                                                       (int)ldo, (int)ldr);
+        gemm_kernel<EPI_LINEAR><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K,
+                                                                       (int)ldo, (int)ldr, dbg);
     }
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;

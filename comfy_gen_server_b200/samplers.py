@@ -512,6 +512,8 @@ class CFGGuider:
         topt["cond_or_uncond"] = list(st["cond_or_uncond"])
         topt["sigmas"] = sigma_vec
         out = m.unet_raw(xc, t_vec, st["context"], st["y"], topt)
+        if not out.is_contiguous():          # channels_last UNets: the 4-channel output is tiny, make it NCHW
+            out = out.contiguous()
         out_u, out_c = self._split_outputs(out, x.shape[0], st)
         return _native.cfg_sampler_tail(x, out_u, out_c, sigma_vec, float(self.cfg), ms.pred_type, old_denoised,
                                         sampler, c0, c1, c2, c3, float(ms.sigma_data))
