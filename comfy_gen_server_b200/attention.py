@@ -223,6 +223,12 @@ class BasicTransformerBlock(nn.Module):
         n = _native.add_layer_norm_(x, a, self.norm2.weight, self.norm2.bias, self.norm2.eps)   # x += a
         a = self.attn2.forward_cross_cached(n, context) if context is not None else self.attn2(n)
         n = _native.add_layer_norm_(x, a, self.norm3.weight, self.norm3.bias, self.norm3.eps)   # x += a
+        ff_out = self.ff.net[2]
+        if isinstance(self.ff.net[0], GEGLU) and not ff_out.comfy_cast_weights and ff_out.weight_function is None \
+                and ff_out.bias_function is None and ff_out.weight.dtype == torch.bfloat16 \
+                and ff_out.weight.shape[0] % 32 == 0:
+            # x = ff.net.2(geglu(n)) + x  with the residual add in the GEMM epilogue, written in place
+            return _native.linear(self.ff.net[0](n), ff_out.weight, ff_out.bias, residual=x, out=x)
         h = self.ff(n)
         h += x
         return h

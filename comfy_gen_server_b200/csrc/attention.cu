@@ -14,9 +14,16 @@
 //   warp  4*NQT+1      TMEM allocator + single-thread tcgen05.mma issuer
 // Per key tile j and query tile t:
 //   S_t = Q_t K_j^T        SS MMA, M=128, N<=128, K=d            -> TMEM  (128 fp32 columns)
-//   softmax warpgroup t:   tcgen05.ld S, running max (lazy: O is only rescaled when the max
-//                          grows by > 2^8), P = exp2(S*scale - m) as bf16 -> tcgen05.st over S
+//   softmax warpgroup t:   tcgen05.ld S into registers and immediately hand the S buffer back (s_free), so the
+//                          tensor core computes S_t(j+1) while this warpgroup is still in softmax(j);
+//                          row max with 3-input FMNMX; lazy running max (O is rescaled only when the max grows
+//                          by > 2^8); x = S*scale - m with packed FFMA2; P = 2^x (MUFU.EX2), row sum with
+//                          packed FADD2, P packed to bf16 -> tcgen05.st into its own TMEM region
 //   O_t += P_t V_j         TS MMA (A = P from TMEM, B = V MN-major from SMEM), fp32 in TMEM
+// TMEM columns: S_t at t*128, P_t at NQT*128 + t*64, O_t at NQT*192 + t*dv_n.
+// (Measured on the way here, profiles/: P aliased over S serialises S(j+1) behind PV(j) and left each
+// warpgroup waiting ~1200 of 3400 cycles per tile; a row-sum MMA against a ones matrix costs a full MMA slot
+// per k-step; ex2.approx.f16x2 is two MUFUs plus a PRMT; kind::f16 rejects fp16 A with bf16 B.)
 // With NQT = 2 the two warpgroups ping-pong: the tensor core works on one tile's MMAs while
 // the other tile is in its softmax. Ragged Nq / Nk and head dims that are not multiples of 64
 // (40, 80, 160) are handled by TMA out-of-bounds zero fill plus column masking; the MMA K/N
@@ -24,6 +31,8 @@
 //
 // Tensor-core bound for self-attention. Algorithmic FLOPs = 4 * B * H * Nq * Nk * d.
 #include "common.cuh"
+
+#include <stdlib.h>
 
 namespace cgs {
 
@@ -35,11 +44,18 @@ constexpr float kRescaleThreshold = 8.0f;  // log2 units
 }  // namespace attn
 
 struct AttnParams {
+    long long* dbg;   // optional timeline buffer (CGS_ATTN_TRACE), nullptr in production
     __nv_bfloat16* out;
+    int tmem_cols;   // power of two >= NQT * (192 + dv_n)
     long long o_stride_b, o_stride_n, o_stride_h;  // elements
     int B, H, Nq, Nk, d;
     float scale_log2;
 };
+
+#define CGS_TRACE(role, j, e)                                                                      \
+    do {                                                                                           \
+        if (p.dbg != nullptr && trace_me && (j) < 64) p.dbg[((role) * 64 + (j)) * 8 + (e)] = clock64(); \
+    } while (0)
 
 template <int NKB, int NQT, int KST>
 struct AttnSmem {
@@ -47,12 +63,12 @@ struct AttnSmem {
     static constexpr int K_OFF = Q_OFF + NQT * NKB * attn::TILE_BYTES;
     static constexpr int V_OFF = K_OFF + KST * NKB * attn::TILE_BYTES;
     static constexpr int BAR_OFF = V_OFF + KST * NKB * attn::TILE_BYTES;
-    static constexpr int NBARS = 3 * NQT + 4 * KST + NQT;
+    static constexpr int NBARS = 5 * NQT + 4 * KST;
     static constexpr int BYTES = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
 template <int NKB, int NQT, int KST>
-__global__ void __launch_bounds__((NQT * 4 + 2) * 32, 1)
+__global__ void __launch_bounds__((NQT * 4 + 2) * 32, (NQT == 1 ? 2 : 1))
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
     using namespace attn;
@@ -65,7 +81,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint64_t* s_full = q_full + NQT;         // [NQT]
     uint64_t* p_full = s_full + NQT;         // [NQT]
     uint64_t* o_full = p_full + NQT;         // [NQT]
-    uint64_t* k_full = o_full + NQT;         // [KST]
+    uint64_t* s_free = o_full + NQT;         // [NQT]
+    uint64_t* k_full = s_free + NQT;         // [KST]
     uint64_t* k_empty = k_full + KST;        // [KST]
     uint64_t* v_full = k_empty + KST;        // [KST]
     uint64_t* v_empty = v_full + KST;        // [KST]
@@ -83,8 +100,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int ksteps_d = (p.d + 15) >> 4;     // K steps of the QK^T MMA
     const int dv_n = ksteps_d << 4;           // N of the PV MMA (d rounded up to 16)
 
-    constexpr uint32_t S_COL = 0;                 // S_t at S_COL + t*128 ; P_t aliases S_t
-    constexpr uint32_t O_COL = NQT * BLOCK_N;     // O_t at O_COL + t*NKB*64
+    constexpr uint32_t S_COL = 0;                 // S_t at t*128
+    constexpr uint32_t P_COL = NQT * BLOCK_N;     // P_t (bf16, 2 per column) at P_COL + t*64
+    constexpr uint32_t O_COL = NQT * 192;         // O_t at O_COL + t*dv_n
+    const uint32_t o_stride = dv_n;
 
     if (warp == PRODUCER_WARP && elect_one()) {
         tma_prefetch_desc(&tmQ);
@@ -98,6 +117,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 mbar_init(&s_full[t], 1);
                 mbar_init(&p_full[t], 128);
                 mbar_init(&o_full[t], 1);
+                mbar_init(&s_free[t], 128);
             }
             for (int s = 0; s < KST; ++s) {
                 mbar_init(&k_full[s], 1);
@@ -108,7 +128,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             fence_mbar_init();
         }
         __syncwarp();
-        tmem_alloc(tmem_slot, 512);
+        tmem_alloc(tmem_slot, p.tmem_cols);
         tmem_relinquish();
     }
     tc_fence_before();
@@ -145,6 +165,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     } else if (warp == MMA_WARP) {
         // ------------------------------------------------------------------ MMA issuer
         if (elect_one()) {
+            const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
             const uint32_t idesc_o = umma_idesc_bf16(BLOCK_M, dv_n, 1);
             auto n_mma_of = [&](int j) {
                 const int valid = min(BLOCK_N, p.Nk - j * BLOCK_N);
@@ -163,8 +184,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 }
             };
             auto issue_pv = [&](int t, int stage, int n_mma, bool accumulate) {
-                const uint32_t d_tmem = tmem_base + O_COL + t * (NKB * 64);
-                const uint32_t a_tmem = tmem_base + S_COL + t * BLOCK_N;
+                const uint32_t d_tmem = tmem_base + O_COL + t * o_stride;
+                const uint32_t a_tmem = tmem_base + P_COL + t * 64;
                 const uint32_t vbase = smem_u32(smem + L::V_OFF + stage * NKB * TILE_BYTES);
                 for (int ks = 0; ks < (n_mma >> 4); ++ks) {
                     // 16 key rows per step = 2 swizzle groups of 8 rows = 2048 bytes;
@@ -190,22 +211,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 int nstage = stage + 1;
                 uint32_t nphase = phase;
                 if (nstage == KST) { nstage = 0; nphase ^= 1; }
-                const bool has_next = (j + 1 < n_tiles);
-                if (has_next) mbar_wait(&k_full[nstage], nphase);
+                if (j + 1 < n_tiles) {
+                    // S(j+1): needs K(j+1) and the S buffer handed back (S(j) copied into registers)
+                    mbar_wait(&k_full[nstage], nphase);
+                    const int n_next = n_mma_of(j + 1);
+                    for (int t = 0; t < NQT; ++t) {
+                        CGS_TRACE(2 + t, j, 0);
+                        mbar_wait(&s_free[t], j & 1);
+                        tc_fence_after();
+                        issue_s(t, nstage, n_next);
+                        tc_commit(&s_full[t]);
+                        CGS_TRACE(2 + t, j, 1);
+                    }
+                    tc_commit(&k_empty[nstage]);
+                }
                 mbar_wait(&v_full[stage], phase);
                 const int n_mma = n_mma_of(j);
                 for (int t = 0; t < NQT; ++t) {
+                    CGS_TRACE(2 + t, j, 2);
                     mbar_wait(&p_full[t], j & 1);
+                    CGS_TRACE(2 + t, j, 3);
                     tc_fence_after();
                     issue_pv(t, stage, n_mma, j > 0);
                     tc_commit(&o_full[t]);
-                    if (t == NQT - 1) tc_commit(&v_empty[stage]);
-                    if (has_next) {
-                        issue_s(t, nstage, n_mma_of(j + 1));
-                        tc_commit(&s_full[t]);
-                        if (t == NQT - 1) tc_commit(&k_empty[nstage]);
-                    }
+                    CGS_TRACE(2 + t, j, 4);
                 }
+                tc_commit(&v_empty[stage]);
                 stage = nstage;
                 phase = nphase;
             }
@@ -218,14 +249,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int row_in_tile = quad * 32 + lane;
         const uint32_t lane_field = static_cast<uint32_t>(quad * 32) << 16;
         const uint32_t s_addr = tmem_base + lane_field + S_COL + t * BLOCK_N;
-        const uint32_t o_addr = tmem_base + lane_field + O_COL + t * (NKB * 64);
+        const uint32_t p_addr = tmem_base + lane_field + P_COL + t * 64;
+        const uint32_t o_addr = tmem_base + lane_field + O_COL + t * o_stride;
 
+        const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && quad == 0 && lane == 0;
         float m_run = -INFINITY;  // running max, already multiplied by scale_log2
         float l_run = 0.f;
         const float scale = p.scale_log2;
+        const uint64_t scale2 = pack_f32x2(scale, scale);
+        if (NQT == 2 && t == 1) named_bar_arrive(2, 256);   // warpgroup 0 goes first
 
         for (int j = 0; j < n_tiles; ++j) {
+            CGS_TRACE(t, j, 0);
             mbar_wait(&s_full[t], j & 1);
+            CGS_TRACE(t, j, 1);
             tc_fence_after();
             uint32_t sr[128];
             tmem_ld_x32(s_addr + 0, sr + 0);
@@ -233,6 +270,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tmem_ld_x32(s_addr + 64, sr + 64);
             tmem_ld_x32(s_addr + 96, sr + 96);
             tmem_wait_ld();
+            // S(j) is in registers: give the buffer back so S(j+1) is computed during this softmax
+            tc_fence_before();
+            mbar_arrive(&s_free[t]);
+            CGS_TRACE(t, j, 2);
 
             const int n_valid = p.Nk - j * BLOCK_N;
             if (n_valid < BLOCK_N) {
@@ -242,13 +283,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
             float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-            for (int i = 0; i < 128; i += 4) {
-                mx0 = fmaxf(mx0, __uint_as_float(sr[i + 0]));
-                mx1 = fmaxf(mx1, __uint_as_float(sr[i + 1]));
-                mx2 = fmaxf(mx2, __uint_as_float(sr[i + 2]));
-                mx3 = fmaxf(mx3, __uint_as_float(sr[i + 3]));
+            for (int i = 0; i < 128; i += 8) {
+                mx0 = fmax3(mx0, __uint_as_float(sr[i + 0]), __uint_as_float(sr[i + 1]));
+                mx1 = fmax3(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
+                mx2 = fmax3(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
+                mx3 = fmax3(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
             }
-            const float m_new = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale;
+            mx0 = fmax3(mx0, mx1, mx2);
+            mx1 = mx3;
+            const float m_new = fmaxf(mx0, mx1) * scale;
 
             float alpha = 1.f;
             bool need_rescale = false;
@@ -260,30 +303,56 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 m_run = m_new;
                 need_rescale = true;
             }
-            const float neg_m = -m_run;
-            float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+            const uint64_t negm2 = pack_f32x2(-m_run, -m_run);
             uint32_t pr[64];
+            uint64_t acc0 = 0ull, acc1 = 0ull;   // two packed (lo, hi) partial row sums
+            CGS_TRACE(t, j, 3);
+            // Only one warpgroup at a time in the exponent section (named barriers 2/3: 128 syncing + 128
+            // arriving threads), so the MUFU serves one warpgroup while the other loads S / finds its max / stores P.
+            if (NQT == 2) named_bar_sync(2 + t, 256);
+            CGS_TRACE(t, j, 6);
+            // phase 1: x = s * scale - m, in place, packed FFMA2
 #pragma unroll
-            for (int i = 0; i < 128; i += 4) {
-                const float e0 = ex2_approx(fmaf(__uint_as_float(sr[i + 0]), scale, neg_m));
-                const float e1 = ex2_approx(fmaf(__uint_as_float(sr[i + 1]), scale, neg_m));
-                const float e2 = ex2_approx(fmaf(__uint_as_float(sr[i + 2]), scale, neg_m));
-                const float e3 = ex2_approx(fmaf(__uint_as_float(sr[i + 3]), scale, neg_m));
-                sum0 += e0; sum1 += e1; sum2 += e2; sum3 += e3;
-                pr[(i >> 1) + 0] = pack_bf16x2(e0, e1);
-                pr[(i >> 1) + 1] = pack_bf16x2(e2, e3);
+            for (int i = 0; i < 64; ++i) {
+                const uint64_t x2 = ffma2(pack_u32x2(sr[2 * i], sr[2 * i + 1]), scale2, negm2);
+                float lo, hi;
+                unpack_f32x2(x2, lo, hi);
+                sr[2 * i] = __float_as_uint(lo);
+                sr[2 * i + 1] = __float_as_uint(hi);
             }
-            l_run += (sum0 + sum1) + (sum2 + sum3);
-
-            // P over the first 64 columns of S (all of S is already in registers)
-            tmem_st_x32(s_addr + 0, pr + 0);
-            tmem_st_x32(s_addr + 32, pr + 32);
-
-            if (__any_sync(0xffffffffu, need_rescale)) {
-                // PV(j-1) has completed by the time S(j) is visible (issue order), so this does
-                // not stall; the wait keeps the ordering explicit.
+            // phase 2: 128 back-to-back MUFU.EX2 (in-order issue: no consumer may sit between them)
+#pragma unroll
+            for (int i = 0; i < 128; ++i) {
+                float y;
+                asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(sr[i])));
+                sr[i] = __float_as_uint(y);
+            }
+            CGS_TRACE(t, j, 7);
+            if (NQT == 2) named_bar_arrive(2 + (t ^ 1), 256);
+            // phase 3: row sum (packed FADD2) and bf16 pack
+#pragma unroll
+            for (int i = 0; i < 64; i += 2) {
+                acc0 = fadd2(acc0, pack_u32x2(sr[2 * i], sr[2 * i + 1]));
+                acc1 = fadd2(acc1, pack_u32x2(sr[2 * i + 2], sr[2 * i + 3]));
+                pr[i] = pack_bf16x2(__uint_as_float(sr[2 * i]), __uint_as_float(sr[2 * i + 1]));
+                pr[i + 1] = pack_bf16x2(__uint_as_float(sr[2 * i + 2]), __uint_as_float(sr[2 * i + 3]));
+            }
+            CGS_TRACE(t, j, 4);
+            {
+                float s0, s1, s2, s3;
+                unpack_f32x2(acc0, s0, s1);
+                unpack_f32x2(acc1, s2, s3);
+                l_run += (s0 + s1) + (s2 + s3);
+            }
+            if (j > 0) {
+                // PV(j-1) must have finished reading P(j-1) (and O must be quiescent for a rescale). It was issued
+                // a whole softmax ago, so this wait is normally already satisfied.
                 mbar_wait(&o_full[t], (j - 1) & 1);
                 tc_fence_after();
+            }
+            tmem_st_x32(p_addr + 0, pr + 0);
+            tmem_st_x32(p_addr + 32, pr + 32);
+            if (__any_sync(0xffffffffu, need_rescale)) {
                 for (int c = 0; c < (dv_n >> 4); ++c) {
                     uint32_t orr[16];
                     tmem_ld_x16(o_addr + c * 16, orr);
@@ -297,6 +366,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(&p_full[t]);
+            CGS_TRACE(t, j, 5);
         }
 
         // epilogue: O / l -> bf16 -> global
@@ -329,7 +399,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
 
     __syncthreads();
-    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 512);
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
 template <int NKB, int NQT, int KST>
@@ -390,6 +460,8 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     if ((rc = make_qkv_map(&tv, v, B, Nk, H, d, v_stride_b, v_stride_n, v_stride_h)) != kOk) return rc;
 
     AttnParams p;
+    p.dbg = nullptr;
+    if (const char* e = getenv("CGS_ATTN_TRACE")) p.dbg = reinterpret_cast<long long*>(strtoull(e, nullptr, 0));
     p.out = static_cast<__nv_bfloat16*>(out);
     p.o_stride_b = o_stride_b;
     p.o_stride_n = o_stride_n;
@@ -397,8 +469,22 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     p.B = B; p.H = H; p.Nq = Nq; p.Nk = Nk; p.d = d;
     p.scale_log2 = softmax_scale * 1.4426950408889634f;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool two_tiles = Nq > attn::BLOCK_M;
-    if (d <= 64) return two_tiles ? launch_attn<1, 2, 3>(tq, tk, tv, p, st) : launch_attn<1, 1, 3>(tq, tk, tv, p, st);
-    if (d <= 128) return two_tiles ? launch_attn<2, 2, 2>(tq, tk, tv, p, st) : launch_attn<2, 1, 2>(tq, tk, tv, p, st);
+    const int dv_n = ((d + 15) / 16) * 16;
+    const int n_tiles = (Nk + attn::BLOCK_N - 1) / attn::BLOCK_N;
+    // Two query tiles per CTA (ping-pong) for long key sequences; one tile per CTA with a single K/V
+    // stage for short ones (text cross-attention, tiny levels): small SMEM/TMEM footprint, 2 CTAs per SM.
+    const bool two_tiles = Nq > attn::BLOCK_M && n_tiles > 2 && 2 * (192 + dv_n) <= 512;
+    const int nqt = two_tiles ? 2 : 1;
+    int cols = 32;
+    while (cols < nqt * (192 + dv_n)) cols *= 2;
+    p.tmem_cols = cols;
+    if (d <= 64) {
+        if (two_tiles) return launch_attn<1, 2, 3>(tq, tk, tv, p, st);
+        return n_tiles > 2 ? launch_attn<1, 1, 3>(tq, tk, tv, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, p, st);
+    }
+    if (d <= 128) {
+        if (two_tiles) return launch_attn<2, 2, 2>(tq, tk, tv, p, st);
+        return n_tiles > 2 ? launch_attn<2, 1, 2>(tq, tk, tv, p, st) : launch_attn<2, 1, 1>(tq, tk, tv, p, st);
+    }
     return launch_attn<3, 1, 1>(tq, tk, tv, p, st);
 }

@@ -59,11 +59,49 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
+// packed fp32x2 helpers (Blackwell FFMA2 / FMNMX3)
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ uint64_t pack_u32x2(uint32_t lo, uint32_t hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+    return r;
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     // cvt.rn.bf16x2.f32 d, a, b  ->  d = {a (upper half), b (lower half)}
     uint32_t r;
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
     return r;
+}
+
+// 2^x for a packed pair of fp32 -> packed bf16x2 (lower half = lo element): 2 x MUFU.EX2 + one pack.
+// (There is no packed half-precision MUFU: ex2.approx.f16x2 lowers to 2 x MUFU.EX2.F16 + PRMT; and
+// kind::f16 MMAs reject mixed fp16 A / bf16 B operands, so P stays bf16 like V.)
+__device__ __forceinline__ uint32_t ex2_bf16x2(uint64_t x2) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x2));
+    return pack_bf16x2(ex2_approx(lo), ex2_approx(hi));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -158,6 +196,9 @@ __device__ __forceinline__ void tma_store_wait_all() {
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------
