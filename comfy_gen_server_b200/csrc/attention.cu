@@ -9,9 +9,11 @@
 // column slices of a fused QKV projection. Output [B, Nq, H, d] bf16. No transposes, no copies.
 //
 // One CTA handles NQT query tiles of 128 rows for one (batch, head):
-//   warps [0, 4*NQT)   softmax warpgroups, one per query tile; thread == query row
-//   warp  4*NQT        TMA producer (Q once; K/V ring of KST stages, 128 keys per tile)
-//   warp  4*NQT+1      TMEM allocator + single-thread tcgen05.mma issuer
+//   warps [0, 4*NQT)          softmax warpgroups, one per query tile; thread == query row
+//   warp  4*NQT               TMA producer (Q once; K/V ring of KST stages, 128 keys per tile)
+//   warps 4*NQT+1 .. +NQT     one single-thread tcgen05.mma issuer per query tile (the first also owns TMEM).
+//                             One issuer for both tiles was the bottleneck of the first versions (~3100 cycles
+//                             of serial issue work per key tile, head-of-line blocking between the tiles).
 // Per key tile j and query tile t:
 //   S_t = Q_t K_j^T        SS MMA, M=128, N<=128, K=d            -> TMEM  (128 fp32 columns)
 //   softmax warpgroup t:   tcgen05.ld S into registers and immediately hand the S buffer back (s_free), so the
@@ -41,6 +43,8 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 128;
 constexpr int TILE_BYTES = 128 * 128;  // one [128 rows x 64 bf16] swizzled box
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
+constexpr int kPolyPairs = 1;    // of every kPolyPeriod element pairs, this many use the FMA-pipe exp2
+constexpr int kPolyPeriod = 4;
 }  // namespace attn
 
 struct AttnParams {
@@ -68,7 +72,7 @@ struct AttnSmem {
 };
 
 template <int NKB, int NQT, int KST>
-__global__ void __launch_bounds__((NQT * 4 + 2) * 32, (NQT == 1 ? 2 : 1))
+__global__ void __launch_bounds__((NQT * 5 + 1) * 32, (NQT == 1 ? 2 : 1))
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
     using namespace attn;
@@ -91,7 +95,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     constexpr int PRODUCER_WARP = NQT * 4;
-    constexpr int MMA_WARP = NQT * 4 + 1;
+    constexpr int MMA_WARP = NQT * 4 + 1;      // first of NQT issuer warps
 
     const int q0 = blockIdx.x * (BLOCK_M * NQT);
     const int head = blockIdx.y;
@@ -121,9 +125,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
             for (int s = 0; s < KST; ++s) {
                 mbar_init(&k_full[s], 1);
-                mbar_init(&k_empty[s], 1);
+                mbar_init(&k_empty[s], NQT);      // one tcgen05.commit per issuer warp
                 mbar_init(&v_full[s], 1);
-                mbar_init(&v_empty[s], 1);
+                mbar_init(&v_empty[s], NQT);
             }
             fence_mbar_init();
         }
@@ -162,47 +166,59 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
         }
         __syncwarp();
-    } else if (warp == MMA_WARP) {
-        // ------------------------------------------------------------------ MMA issuer
+    } else if (warp >= MMA_WARP) {
+        // ------------------------------------------------------------------ MMA issuer for query tile t
         if (elect_one()) {
+            const int t = warp - MMA_WARP;
             const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
             const uint32_t idesc_o = umma_idesc_bf16(BLOCK_M, dv_n, 1);
+            // descriptor halves: K-major operands (Q, K): LBO 16 B, SBO 1024 B; MN-major V: LBO = one TMA box
+            const uint64_t dk = umma_desc_sw128(0, 16, 1024);
+            const uint64_t dvv = umma_desc_sw128(0, TILE_BYTES, 1024);
+            const uint32_t hi_k = static_cast<uint32_t>(dk >> 32), hi_v = static_cast<uint32_t>(dvv >> 32);
+            // low word = start address >> 4 in bits [0,14) and the leading-dimension byte offset >> 4 in bits [16,30)
+            const uint32_t q_lo = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::Q_OFF + t * NKB * TILE_BYTES) & 0x3FFFF) >> 4);
+            const uint32_t k_lo0 = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::K_OFF) & 0x3FFFF) >> 4);
+            const uint32_t v_lo0 = static_cast<uint32_t>(dvv) | ((smem_u32(smem + L::V_OFF) & 0x3FFFF) >> 4);
+            constexpr uint32_t STAGE_LO = (NKB * TILE_BYTES) >> 4;
+            const uint32_t s_tmem = tmem_base + S_COL + t * BLOCK_N;
+            const uint32_t p_tmem = tmem_base + P_COL + t * 64;
+            const uint32_t o_tmem = tmem_base + O_COL + t * o_stride;
             auto n_mma_of = [&](int j) {
                 const int valid = min(BLOCK_N, p.Nk - j * BLOCK_N);
                 return (valid + 15) & ~15;
             };
-            auto issue_s = [&](int t, int stage, int n_mma) {
+            auto issue_s = [&](int stage, int n_mma) {
                 const uint32_t idesc_s = umma_idesc_bf16(BLOCK_M, n_mma, 0);
-                const uint32_t d_tmem = tmem_base + S_COL + t * BLOCK_N;
-                for (int s = 0; s < ksteps_d; ++s) {
-                    const int kb = s >> 2, k = s & 3;
-                    const uint64_t adesc = umma_desc_sw128(
-                        smem_u32(smem + L::Q_OFF + (t * NKB + kb) * TILE_BYTES) + 32 * k, 16, 1024);
-                    const uint64_t bdesc = umma_desc_sw128(
-                        smem_u32(smem + L::K_OFF + (stage * NKB + kb) * TILE_BYTES) + 32 * k, 16, 1024);
-                    umma_ss(d_tmem, adesc, bdesc, idesc_s, s != 0);
+                const uint32_t k_lo = k_lo0 + stage * STAGE_LO;
+#pragma unroll
+                for (int s = 0; s < NKB * 4; ++s) {
+                    if (s < ksteps_d) {
+                        // 64-wide block kb = s / 4 (one TMA box, TILE_BYTES apart), 32 bytes per k-step inside it
+                        const uint32_t off = (s >> 2) * (TILE_BYTES >> 4) + (s & 3) * 2;
+                        umma_ss_lh(s_tmem, q_lo + off, hi_k, k_lo + off, hi_k, idesc_s, s != 0);
+                    }
                 }
             };
-            auto issue_pv = [&](int t, int stage, int n_mma, bool accumulate) {
-                const uint32_t d_tmem = tmem_base + O_COL + t * o_stride;
-                const uint32_t a_tmem = tmem_base + P_COL + t * 64;
-                const uint32_t vbase = smem_u32(smem + L::V_OFF + stage * NKB * TILE_BYTES);
-                for (int ks = 0; ks < (n_mma >> 4); ++ks) {
-                    // 16 key rows per step = 2 swizzle groups of 8 rows = 2048 bytes;
-                    // LBO = distance between 64-wide head-dim blocks (one TMA box).
-                    const uint64_t bdesc = umma_desc_sw128(vbase + ks * 2048, TILE_BYTES, 1024);
-                    umma_ts(d_tmem, a_tmem + ks * 8, bdesc, idesc_o, (accumulate || ks != 0) ? 1u : 0u);
+            auto issue_pv = [&](int stage, int n_mma, uint32_t accumulate) {
+                const uint32_t v_lo = v_lo0 + stage * STAGE_LO;
+                const int ksteps = n_mma >> 4;
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    if (ks < ksteps) {
+                        // 16 key rows per step = 2 swizzle groups of 8 rows = 2048 bytes
+                        umma_ts_lh(o_tmem, p_tmem + ks * 8, v_lo + ks * (2048 >> 4), hi_v, idesc_o,
+                                   (accumulate | ks) != 0 ? 1u : 0u);
+                    }
                 }
             };
 
-            // prologue: S_t(0) for every query tile
+            // prologue: S_t(0)
+            mbar_wait(&q_full[t], 0);
             mbar_wait(&k_full[0], 0);
-            for (int t = 0; t < NQT; ++t) {
-                mbar_wait(&q_full[t], 0);
-                tc_fence_after();
-                issue_s(t, 0, n_mma_of(0));
-                tc_commit(&s_full[t]);
-            }
+            tc_fence_after();
+            issue_s(0, n_mma_of(0));
+            tc_commit(&s_full[t]);
             tc_commit(&k_empty[0]);
 
             int stage = 0;
@@ -214,29 +230,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (j + 1 < n_tiles) {
                     // S(j+1): needs K(j+1) and the S buffer handed back (S(j) copied into registers)
                     mbar_wait(&k_full[nstage], nphase);
-                    const int n_next = n_mma_of(j + 1);
-                    for (int t = 0; t < NQT; ++t) {
-                        CGS_TRACE(2 + t, j, 0);
-                        mbar_wait(&s_free[t], j & 1);
-                        tc_fence_after();
-                        issue_s(t, nstage, n_next);
-                        tc_commit(&s_full[t]);
-                        CGS_TRACE(2 + t, j, 1);
-                    }
+                    CGS_TRACE(2 + t, j, 0);
+                    mbar_wait(&s_free[t], j & 1);
+                    tc_fence_after();
+                    issue_s(nstage, n_mma_of(j + 1));
+                    tc_commit(&s_full[t]);
                     tc_commit(&k_empty[nstage]);
+                    CGS_TRACE(2 + t, j, 1);
                 }
                 mbar_wait(&v_full[stage], phase);
-                const int n_mma = n_mma_of(j);
-                for (int t = 0; t < NQT; ++t) {
-                    CGS_TRACE(2 + t, j, 2);
-                    mbar_wait(&p_full[t], j & 1);
-                    CGS_TRACE(2 + t, j, 3);
-                    tc_fence_after();
-                    issue_pv(t, stage, n_mma, j > 0);
-                    tc_commit(&o_full[t]);
-                    CGS_TRACE(2 + t, j, 4);
-                }
+                CGS_TRACE(2 + t, j, 2);
+                mbar_wait(&p_full[t], j & 1);
+                CGS_TRACE(2 + t, j, 3);
+                tc_fence_after();
+                issue_pv(stage, n_mma_of(j), j > 0 ? 1u : 0u);
+                tc_commit(&o_full[t]);
                 tc_commit(&v_empty[stage]);
+                CGS_TRACE(2 + t, j, 4);
                 stage = nstage;
                 phase = nphase;
             }
@@ -257,7 +267,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         float l_run = 0.f;
         const float scale = p.scale_log2;
         const uint64_t scale2 = pack_f32x2(scale, scale);
-        if (NQT == 2 && t == 1) named_bar_arrive(2, 256);   // warpgroup 0 goes first
 
         for (int j = 0; j < n_tiles; ++j) {
             CGS_TRACE(t, j, 0);
@@ -307,10 +316,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             uint32_t pr[64];
             uint64_t acc0 = 0ull, acc1 = 0ull;   // two packed (lo, hi) partial row sums
             CGS_TRACE(t, j, 3);
-            // Only one warpgroup at a time in the exponent section (named barriers 2/3: 128 syncing + 128
-            // arriving threads), so the MUFU serves one warpgroup while the other loads S / finds its max / stores P.
-            if (NQT == 2) named_bar_sync(2 + t, 256);
-            CGS_TRACE(t, j, 6);
             // phase 1: x = s * scale - m, in place, packed FFMA2
 #pragma unroll
             for (int i = 0; i < 64; ++i) {
@@ -320,15 +325,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 sr[2 * i] = __float_as_uint(lo);
                 sr[2 * i + 1] = __float_as_uint(hi);
             }
-            // phase 2: 128 back-to-back MUFU.EX2 (in-order issue: no consumer may sit between them)
+            CGS_TRACE(t, j, 6);
+            // phase 2: 2^x. The MUFU (16 lanes/clk/SM, ~12 clk per warp instruction in situ) is the limiter of
+            // d = 64 attention, so kPolyPairs of every kPolyPeriod pairs are evaluated on the FMA pipe instead.
+            // All pairs are independent: the two pipes run side by side.
 #pragma unroll
-            for (int i = 0; i < 128; ++i) {
-                float y;
-                asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(__uint_as_float(sr[i])));
-                sr[i] = __float_as_uint(y);
+            for (int i = 0; i < 64; ++i) {
+                if ((i % kPolyPeriod) < kPolyPairs) {
+                    uint32_t rlo, rhi;
+                    const uint64_t r = ex2_poly2(pack_u32x2(sr[2 * i], sr[2 * i + 1]));
+                    asm("mov.b64 {%0, %1}, %2;" : "=r"(rlo), "=r"(rhi) : "l"(r));
+                    sr[2 * i] = rlo;
+                    sr[2 * i + 1] = rhi;
+                } else {
+                    sr[2 * i] = __float_as_uint(ex2_approx(__uint_as_float(sr[2 * i])));
+                    sr[2 * i + 1] = __float_as_uint(ex2_approx(__uint_as_float(sr[2 * i + 1])));
+                }
             }
             CGS_TRACE(t, j, 7);
-            if (NQT == 2) named_bar_arrive(2 + (t ^ 1), 256);
             // phase 3: row sum (packed FADD2) and bf16 pack
 #pragma unroll
             for (int i = 0; i < 64; i += 2) {
@@ -409,7 +423,7 @@ static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUten
     auto kern = attn_fwd_kernel<NKB, NQT, KST>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
     dim3 grid((p.Nq + attn::BLOCK_M * NQT - 1) / (attn::BLOCK_M * NQT), p.H, p.B);
-    kern<<<grid, (NQT * 4 + 2) * 32, L::BYTES, stream>>>(tq, tk, tv, p);
+    kern<<<grid, (NQT * 5 + 1) * 32, L::BYTES, stream>>>(tq, tk, tv, p);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }

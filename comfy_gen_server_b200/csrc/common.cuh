@@ -83,6 +83,32 @@ __device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
 __device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
     asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
 }
+// 2^x for a packed pair on the FMA pipe instead of the MUFU (FlashAttention-4's trick): round-to-nearest range
+// reduction with the 1.5 * 2^23 magic constant, degree-3 minimax polynomial on [-0.5, 0.5] (max rel. error
+// 7.5e-5, far below the bf16 rounding P gets anyway), exponent added in the integer domain. x must be <= ~120;
+// inputs are clamped at -125 (result ~2^-125).
+__device__ __forceinline__ uint64_t ex2_poly2(uint64_t x2) {
+    float lo, hi;
+    unpack_f32x2(x2, lo, hi);
+    lo = fmaxf(lo, -125.0f);
+    hi = fmaxf(hi, -125.0f);
+    const uint64_t xc = pack_f32x2(lo, hi);
+    const uint64_t magic = pack_f32x2(12582912.0f, 12582912.0f);
+    const uint64_t neg_magic = pack_f32x2(-12582912.0f, -12582912.0f);
+    const uint64_t t = fadd2(xc, magic);                                   // integer part in the low mantissa bits
+    const uint64_t n = fadd2(t, neg_magic);                                // round(x) as float
+    const uint64_t f = ffma2(n, pack_f32x2(-1.0f, -1.0f), xc);             // x - round(x)
+    uint64_t p = ffma2(pack_f32x2(0.05517147481441498f, 0.05517147481441498f), f,
+                       pack_f32x2(0.242610901594162f, 0.242610901594162f));
+    p = ffma2(p, f, pack_f32x2(0.6932609677314758f, 0.6932609677314758f));
+    p = ffma2(p, f, pack_f32x2(0.9999281167984009f, 0.9999281167984009f));
+    uint32_t plo, phi, tlo, thi;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(plo), "=r"(phi) : "l"(p));
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(tlo), "=r"(thi) : "l"(t));
+    plo += tlo << 23;
+    phi += thi << 23;
+    return pack_u32x2(plo, phi);
+}
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
@@ -259,6 +285,37 @@ __device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
         "}\n"
         ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// Same MMAs with the 64-bit shared-memory descriptor passed as two 32-bit halves: the high word (LBO/SBO/
+// version/swizzle) is loop-invariant and the low word only needs 32-bit adds, which keeps the single issuing
+// thread's dependent instruction chain short.
+__device__ __forceinline__ void umma_ss_lh(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                           uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
+        "}\n"
+        ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_ts_lh(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi,
+                                           uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 db;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t"
+        "}\n"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 

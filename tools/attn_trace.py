@@ -13,7 +13,7 @@ torch.cuda.synchronize()
 t = buf.cpu().view(4, 64, 8)
 t0 = int(t[t > 0].min())
 names = ["WG0", "WG1", "MMA0", "MMA1"]
-for j in list(range(0, 6)) + list(range(20, 24)):
+for j in list(range(10, 14)):
     for r in range(4):
         row = [(int(x) - t0) if x > 0 else -1 for x in t[r, j]]
         print(f"j={j:2d} {names[r]:5s} " + " ".join(f"{x:7d}" for x in row[:7]))
