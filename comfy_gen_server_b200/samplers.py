@@ -568,12 +568,25 @@ class SplitCFGGuider(CFGGuider):
         self.placement = placement
         self.group = group
 
-    def _select_parts(self, parts, use_uncond):
-        if not use_uncond:
+    def _build_fused(self, x, model_options):
+        """Build the batched [uncond, cond] conditioning exactly as the unsplit guider does (including the LCM
+        repeat-padding of mismatched text lengths, comfy/conds.py:50-63), then keep only this rank's half, so a
+        split run sees the same per-sample inputs as the batched run."""
+        st = super()._build_fused(x, model_options)
+        if st is None:
+            return None
+        if st["copies"] != 2:
             raise RuntimeError("cfg_split placement needs cfg != 1 (there is no uncond half to split off)")
-        if self.placement.role == "uncond":
-            return [parts[0]], [1]
-        return [parts[1]], [0]
+        b = st["batch"]
+        half = slice(0, b) if self.placement.role == "uncond" else slice(b, 2 * b)
+        st["context"] = st["context"][half].contiguous()
+        if st["y"] is not None:
+            st["y"] = st["y"][half].contiguous()
+        if st["tables"] is not None:
+            st["tables"] = (st["tables"][0], st["tables"][1][:, :b].contiguous(), st["tables"][2])
+        st["copies"] = 1
+        st["cond_or_uncond"] = [1] if self.placement.role == "uncond" else [0]
+        return st
 
     def _split_outputs(self, out, b, st):
         return model_management.exchange_cfg_halves(out, self.placement, self.group)
