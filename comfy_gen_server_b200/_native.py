@@ -25,6 +25,7 @@ _SIGNATURES = {
     "cgs_attention_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 12 + [_c_float, _c_void_p],
     "cgs_layernorm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_add_layernorm_fwd": [_c_void_p] * 6 + [_c_ll, _c_int, _c_float, _c_void_p],
+    "cgs_groupnorm_fwd": [_c_void_p] * 4 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
@@ -204,6 +205,23 @@ def add_layer_norm_(x: torch.Tensor, residual: torch.Tensor, weight: torch.Tenso
                                                   bias.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, eps,
                                                   _stream(x))
     _check(rc, "cgs_add_layernorm_fwd")
+    return y
+
+
+def group_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, groups: int, eps: float,
+               silu: bool = False) -> torch.Tensor:
+    """GroupNorm over NCHW (+ fused SiLU). x [N, C, H, W] bf16 contiguous."""
+    _require_cuda("group_norm x", x, torch.bfloat16)
+    _require_cuda("group_norm weight", weight, torch.bfloat16)
+    _require_cuda("group_norm bias", bias, torch.bfloat16)
+    if x.dim() != 4 or not x.is_contiguous():
+        raise RuntimeError("group_norm: expected a contiguous [N, C, H, W] tensor")
+    n, c, h, w = x.shape
+    y = torch.empty_like(x)
+    with _Launch("groupnorm", x, 4.0 * x.numel()):
+        rc = load_library().cgs_groupnorm_fwd(x.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+                                              n, c, h * w, groups, eps, int(silu), _stream(x))
+    _check(rc, "cgs_groupnorm_fwd")
     return y
 
 

@@ -117,14 +117,28 @@ class b200_ops:
         def reset_parameters(self):
             return None
 
-        def forward_comfy_cast_weights(self, input):
-            weight, bias = cast_bias_weight(self, input)
-            return torch.nn.functional.group_norm(input, self.num_groups, weight, bias, self.eps)
+        def native_ok(self, input):
+            return (_native_ok(input) and input.dim() == 4 and input.is_contiguous() and self.affine
+                    and (input.shape[2] * input.shape[3]) % 8 == 0)
 
-        def forward(self, *args, **kwargs):
+        def forward_fused(self, input, silu=False):
+            """GroupNorm with the SiLU that follows it in a ResBlock fused in (cgs_groupnorm_fwd) when the tensor
+            is a contiguous NCHW bf16 CUDA tensor; otherwise the reference's F.group_norm (+ F.silu) library path,
+            which is what the reference runs for this op."""
             if self.comfy_cast_weights:
-                return self.forward_comfy_cast_weights(*args, **kwargs)
-            return super().forward(*args, **kwargs)
+                weight, bias = cast_bias_weight(self, input)
+            else:
+                weight, bias = self.weight, self.bias
+            if self.native_ok(input) and weight.dtype == torch.bfloat16:
+                return _native.group_norm(input, weight, bias, self.num_groups, self.eps, silu)
+            out = torch.nn.functional.group_norm(input, self.num_groups, weight, bias, self.eps)
+            return torch.nn.functional.silu(out) if silu else out
+
+        def forward_comfy_cast_weights(self, input):
+            return self.forward_fused(input, False)
+
+        def forward(self, input):
+            return self.forward_fused(input, False)
 
     class ConvTranspose2d(torch.nn.ConvTranspose2d, CastWeightBiasOp):
         def reset_parameters(self):

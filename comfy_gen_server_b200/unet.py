@@ -36,6 +36,15 @@ class TimestepBlock(nn.Module):
     pass
 
 
+def _norm_silu(norm, x):
+    """GroupNorm -> SiLU (the first two layers of ResBlock.in_layers / out_layers and of UNetModel.out), fused
+    into one kernel when the norm is the B200 operator class."""
+    fused = getattr(norm, "forward_fused", None)
+    if fused is not None:
+        return fused(x, True)
+    return F.silu(norm(x))
+
+
 class Upsample(nn.Module):
     """openaimodel.py:60-96 (2-D, nearest, optional 3x3 conv)."""
     def __init__(self, channels, use_conv, dims=2, out_channels=None, padding=1, dtype=None, device=None,
@@ -96,10 +105,10 @@ class ResBlock(TimestepBlock):
             self.skip_connection = operations.conv_nd(dims, channels, self.out_channels, 1, dtype=dtype, device=device)
 
     def forward(self, x, emb):
-        h = self.in_layers(x)
+        h = self.in_layers[2](_norm_silu(self.in_layers[0], x))
         emb_out = self.emb_layers(emb).type(h.dtype)
         h = h + emb_out[..., None, None]
-        h = self.out_layers(h)
+        h = self.out_layers[3](self.out_layers[2](_norm_silu(self.out_layers[0], h)))
         return self.skip_connection(x) + h
 
 
@@ -278,4 +287,4 @@ class UNetModel(nn.Module):
             output_shape = hs[-1].shape if len(hs) > 0 else None
             h = forward_timestep_embed(module, h, emb, context, transformer_options, output_shape)
         h = h.type(x.dtype)
-        return self.out(h)
+        return self.out[2](_norm_silu(self.out[0], h))

@@ -73,6 +73,16 @@ int cgs_add_layernorm_fwd(const void* x, const void* residual, const void* gamma
                           long long rows, int C, float eps, void* stream);
 
 /*
+ * GroupNorm (+ optional fused SiLU), NCHW. Replaces ops.GroupNorm -> F.group_norm and the nn.SiLU that follows
+ * it in ResBlock.in_layers / out_layers and UNetModel.out
+ * (comfy/ldm/modules/diffusionmodules/openaimodel.py:177-181, 213-217, 805-807), and SpatialTransformer.norm
+ * (comfy/ldm/modules/attention.py:595; silu = 0, eps = 1e-6).
+ *   x, y [N, C, H*W] bf16 contiguous; gamma, beta [C] bf16; C % groups == 0; H*W % 8 == 0; fp32 statistics.
+ */
+int cgs_groupnorm_fwd(const void* x, const void* gamma, const void* beta, void* y,
+                      int N, int C, int HW, int groups, float eps, int silu, void* stream);
+
+/*
  * GEGLU projection (G1): y[m, n] = (x W^T + b)[m, n] * gelu_erf((x W^T + b)[m, N + n]).
  * Replaces GEGLU.forward: Linear -> chunk(2) -> F.gelu -> mul
  * (comfy/ldm/modules/attention.py:56-63).

@@ -141,6 +141,29 @@ def test_layernorm_errors_and_empty():
     assert n.layer_norm(bf(torch.ones(0, 16)), bf(torch.ones(16)), bf(torch.ones(16))).shape == (0, 16)
 
 
+# ------------------------------------------------------------------------------------------ GroupNorm
+@pytest.mark.parametrize("N_,C,H,W,silu", [(2, 320, 32, 32, True), (2, 640, 16, 16, True), (1, 1280, 8, 8, False),
+                                           (3, 64, 12, 12, True), (2, 960, 16, 16, True), (1, 32, 2, 4, False)])
+def test_groupnorm_silu_vs_oracle(N_, C, H, W, silu):
+    x = bf(randn((N_, C, H, W), 1, 2.0) + 0.5)
+    w, b = bf(randn((C,), 2) * 0.2 + 1), bf(randn((C,), 3) * 0.2)
+    eps = 1e-5 if silu else 1e-6
+    y = N().group_norm(x, w, b, 32, eps, silu).float().cpu()
+    ref = torch.nn.functional.group_norm(x.float().cpu(), 32, w.float().cpu(), b.float().cpu(), eps)
+    if silu:
+        ref = torch.nn.functional.silu(ref)
+    assert (y - ref).abs().max() <= ulp_tol(ref)
+
+
+def test_groupnorm_errors():
+    n = N()
+    w = bf(torch.ones(64))
+    with pytest.raises(RuntimeError):
+        n.group_norm(bf(torch.ones(1, 64, 3, 3)), w, w, 32, 1e-5)          # H*W % 8 != 0
+    with pytest.raises(RuntimeError):
+        n.group_norm(torch.ones(1, 64, 4, 4), w.cpu(), w.cpu(), 32, 1e-5)   # CPU tensor
+
+
 # ------------------------------------------------------------------------------------------ GEMMs
 @pytest.mark.parametrize("M,K,Nn", [(128, 64, 128), (300, 320, 1280), (2 * 1024, 640, 2560), (2 * 256, 1280, 5120),
                                     (1, 128, 128), (4096 + 17, 320, 1280)])
