@@ -487,14 +487,17 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     const int n_tiles = (Nk + attn::BLOCK_N - 1) / attn::BLOCK_N;
     // Two query tiles per CTA (ping-pong) for long key sequences; one tile per CTA with a single K/V
     // stage for short ones (text cross-attention, tiny levels): small SMEM/TMEM footprint, 2 CTAs per SM.
-    const bool two_tiles = Nq > attn::BLOCK_M && n_tiles > 2 && 2 * (192 + dv_n) <= 512;
+    bool two_tiles = Nq > attn::BLOCK_M && n_tiles > 2 && 2 * (192 + dv_n) <= 512;
+    if (const char* e = getenv("CGS_ATTN_MAX_TILES_1CTA")) {     // experiment knob: one query tile per CTA up to this many key tiles
+        if (n_tiles <= atoi(e)) two_tiles = false;
+    }
     const int nqt = two_tiles ? 2 : 1;
     int cols = 32;
     while (cols < nqt * (192 + dv_n)) cols *= 2;
     p.tmem_cols = cols;
     if (d <= 64) {
         if (two_tiles) return launch_attn<1, 2, 3>(tq, tk, tv, p, st);
-        return n_tiles > 2 ? launch_attn<1, 1, 3>(tq, tk, tv, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, p, st);
+        return n_tiles > 2 ? launch_attn<1, 1, 2>(tq, tk, tv, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, p, st);
     }
     if (d <= 128) {
         if (two_tiles) return launch_attn<2, 2, 2>(tq, tk, tv, p, st);
