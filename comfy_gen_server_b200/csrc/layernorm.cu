@@ -31,9 +31,10 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// MAXV = max 16-byte vectors per lane  (C <= 256 * MAXV).
+// MAXV = max 16-byte vectors per lane  (C <= 256 * MAXV). The row is kept in registers as packed bf16 (4 registers
+// per 8 elements) and unpacked in each of the three passes: fewer registers -> 4 blocks (32 rows) per SM in flight.
 template <int MAXV, bool ADD_RESIDUAL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (MAXV <= 5 ? 4 : 2))
 layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
                  const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
                  __nv_bfloat16* x_out, __nv_bfloat16* __restrict__ y, long long rows,
@@ -45,29 +46,34 @@ layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
     const Vec8* xr = reinterpret_cast<const Vec8*>(x + row * C);
     const Vec8* rr = ADD_RESIDUAL ? reinterpret_cast<const Vec8*>(res + row * C) : nullptr;
 
-    float f[MAXV][8];
-    float sum = 0.f;
+    Vec8 a[MAXV];
+    Vec8 r[ADD_RESIDUAL ? MAXV : 1];
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
         const int v = lane + i * 32;
         if (v < nvec) {
             // x_out may alias x (in-place residual update): plain loads on that path.
-            Vec8 a = ADD_RESIDUAL ? xr[v] : ld_stream(xr + v);
+            a[i] = ADD_RESIDUAL ? xr[v] : ld_stream(xr + v);
+            if (ADD_RESIDUAL) r[i] = ld_stream(rr + v);
+        }
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int v = lane + i * 32;
+        if (v < nvec) {
             if (ADD_RESIDUAL) {
-                Vec8 b = rr[v];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     // the reference adds in bf16 (x += n on bf16 tensors): round the sum to bf16
                     // before normalising, and store it as the new residual stream.
-                    a.v[j] = __hadd2_rn(a.v[j], b.v[j]);
+                    a[i].v[j] = __hadd2_rn(a[i].v[j], r[i].v[j]);
                 }
-                reinterpret_cast<Vec8*>(x_out + row * C)[v] = a;
+                reinterpret_cast<Vec8*>(x_out + row * C)[v] = a[i];
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                float2 t = __bfloat1622float2(a.v[j]);
-                f[i][2 * j] = t.x;
-                f[i][2 * j + 1] = t.y;
+                const float2 t = __bfloat1622float2(a[i].v[j]);
                 sum += t.x + t.y;
             }
         }
@@ -78,9 +84,10 @@ layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
     for (int i = 0; i < MAXV; ++i) {
         if (lane + i * 32 < nvec) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float d = f[i][j] - mean;
-                sq += d * d;
+            for (int j = 0; j < 4; ++j) {
+                const float2 t = __bfloat1622float2(a[i].v[j]);
+                const float d0 = t.x - mean, d1 = t.y - mean;
+                sq += d0 * d0 + d1 * d1;
             }
         }
     }
@@ -93,15 +100,16 @@ layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
     for (int i = 0; i < MAXV; ++i) {
         const int v = lane + i * 32;
         if (v < nvec) {
-            Vec8 g = g8[v];
-            Vec8 b = b8[v];
+            const Vec8 g = g8[v];
+            const Vec8 b = b8[v];
             Vec8 o;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
+                const float2 t = __bfloat1622float2(a[i].v[j]);
                 const float2 gg = __bfloat1622float2(g.v[j]);
                 const float2 bb = __bfloat1622float2(b.v[j]);
-                const float o0 = (f[i][2 * j] - mean) * rstd * gg.x + bb.x;
-                const float o1 = (f[i][2 * j + 1] - mean) * rstd * gg.y + bb.y;
+                const float o0 = (t.x - mean) * rstd * gg.x + bb.x;
+                const float o1 = (t.y - mean) * rstd * gg.y + bb.y;
                 o.v[j] = __floats2bfloat162_rn(o0, o1);
             }
             yr[v] = o;
