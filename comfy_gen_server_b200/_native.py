@@ -403,6 +403,7 @@ def register_torch_ops() -> None:
     lib = torch.library.Library("cgs_b200", "DEF")
     lib.define("attention(Tensor q, Tensor k, Tensor v, int heads) -> Tensor")
     lib.define("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps) -> Tensor")
+    lib.define("group_norm(Tensor x, Tensor weight, Tensor bias, int groups, float eps, bool silu) -> Tensor")
     lib.define("geglu(Tensor x, Tensor weight, Tensor? bias) -> Tensor")
     lib.define("linear(Tensor x, Tensor weight, Tensor? bias, Tensor? residual) -> Tensor")
     lib.define("cfg_denoise(Tensor x, Tensor? out_uncond, Tensor out_cond, Tensor sigma, float cond_scale, "
@@ -413,6 +414,7 @@ def register_torch_ops() -> None:
 
     lib.impl("attention", attention, "CUDA")
     lib.impl("layer_norm", layer_norm, "CUDA")
+    lib.impl("group_norm", group_norm, "CUDA")
     lib.impl("geglu", geglu, "CUDA")
     lib.impl("linear", lambda x, w, b, r: linear(x, w, b, r), "CUDA")
     lib.impl("cfg_denoise", lambda x, u, c, s, cs, pt: cfg_denoise(x, u, c, s, cs, pt), "CUDA")
@@ -422,6 +424,7 @@ def register_torch_ops() -> None:
 
     lib.impl("attention", lambda q, k, v, heads: torch.empty_like(q), "Meta")
     lib.impl("layer_norm", lambda x, w, b, eps: torch.empty_like(x), "Meta")
+    lib.impl("group_norm", lambda x, w, b, g, eps, silu: torch.empty_like(x), "Meta")
     lib.impl("geglu", lambda x, w, b: x.new_empty((*x.shape[:-1], w.shape[0] // 2)), "Meta")
     lib.impl("linear", lambda x, w, b, r: x.new_empty((*x.shape[:-1], w.shape[0])), "Meta")
     lib.impl("cfg_denoise", lambda x, u, c, s, cs, pt: torch.empty_like(x), "Meta")

@@ -216,3 +216,31 @@ def test_unet_layout_matches_reference_key_names():
 def uc_shapes(fam):
     from comfy_gen_server_b200 import unet_config as uc
     return uc.param_shapes(uc.FAMILIES[fam]["unet"])
+
+
+def test_install_into_reference_tree_rebinds_and_restores():
+    """Drop-in check against the real reference (only where /root/reference exists, i.e. the build container)."""
+    ref = os.environ.get("CGS_REFERENCE", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "comfy")):
+        pytest.skip("reference tree not present on this machine")
+    code = r'''
+import sys, types
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+sys.modules["torchsde"] = types.ModuleType("torchsde")
+import comfy.cli_args; comfy.cli_args.args.cpu = True
+import comfy.ldm.modules.attention as ra, comfy.k_diffusion.sampling as rk, comfy.ops as ro
+import comfy_gen_server_b200.integration as b200
+orig = (ra.optimized_attention, rk.sample_euler, ro.disable_weight_init.LayerNorm.forward, ra.GEGLU.forward)
+log = b200.install()
+from comfy_gen_server_b200.attention import attention_b200
+assert ra.optimized_attention is attention_b200 and ra.optimized_attention_masked is attention_b200
+assert rk.sample_dpmpp_2m.__module__.startswith("comfy_gen_server_b200") and len(log) >= 9
+import comfy.samplers as rs
+assert rs.ksampler("dpmpp_2m").sampler_function is rk.sample_dpmpp_2m      # getattr lookup sees the new function
+b200.uninstall()
+assert (ra.optimized_attention, rk.sample_euler, ro.disable_weight_init.LayerNorm.forward, ra.GEGLU.forward) == orig
+print("OK")
+''' % (ref, ROOT)
+    import subprocess
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and "OK" in p.stdout, p.stdout[-1500:] + p.stderr[-1500:]
