@@ -25,7 +25,8 @@ _SIGNATURES = {
     "cgs_attention_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 12 + [_c_float, _c_void_p],
     "cgs_layernorm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_add_layernorm_fwd": [_c_void_p] * 6 + [_c_ll, _c_int, _c_float, _c_void_p],
-    "cgs_groupnorm_fwd": [_c_void_p] * 4 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
+    "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
+    "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
@@ -209,20 +210,45 @@ def add_layer_norm_(x: torch.Tensor, residual: torch.Tensor, weight: torch.Tenso
 
 
 def group_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, groups: int, eps: float,
-               silu: bool = False) -> torch.Tensor:
-    """GroupNorm over NCHW (+ fused SiLU). x [N, C, H, W] bf16 contiguous."""
+               silu: bool = False, add_nc: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """GroupNorm over NCHW (+ fused SiLU, + a per-(sample, channel) addend applied first). x [N, C, H, W] bf16."""
     _require_cuda("group_norm x", x, torch.bfloat16)
     _require_cuda("group_norm weight", weight, torch.bfloat16)
     _require_cuda("group_norm bias", bias, torch.bfloat16)
     if x.dim() != 4 or not x.is_contiguous():
         raise RuntimeError("group_norm: expected a contiguous [N, C, H, W] tensor")
     n, c, h, w = x.shape
+    a_ptr = None
+    if add_nc is not None:
+        _require_cuda("group_norm add_nc", add_nc, torch.bfloat16)
+        if add_nc.shape != (n, c) or not add_nc.is_contiguous():
+            raise RuntimeError("group_norm: add_nc must be a contiguous [N, C] tensor")
+        a_ptr = add_nc.data_ptr()
     y = torch.empty_like(x)
     with _Launch("groupnorm", x, 4.0 * x.numel()):
-        rc = load_library().cgs_groupnorm_fwd(x.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+        rc = load_library().cgs_groupnorm_fwd(x.data_ptr(), a_ptr, weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
                                               n, c, h * w, groups, eps, int(silu), _stream(x))
     _check(rc, "cgs_groupnorm_fwd")
     return y
+
+
+def transpose_add(x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[n, c, r] = x[n, r, c] (+ residual[n, c, r]); x [N, R, C] bf16 contiguous -> [N, C, R]."""
+    _require_cuda("transpose_add x", x, torch.bfloat16)
+    if x.dim() != 3 or not x.is_contiguous():
+        raise RuntimeError("transpose_add: expected a contiguous [N, R, C] tensor")
+    n, r, c = x.shape
+    r_ptr = None
+    if residual is not None:
+        _require_cuda("transpose_add residual", residual, torch.bfloat16)
+        if residual.numel() != x.numel() or not residual.is_contiguous():
+            raise RuntimeError("transpose_add: residual must be contiguous with the output's shape")
+        r_ptr = residual.data_ptr()
+    out = torch.empty((n, c, r), dtype=torch.bfloat16, device=x.device)
+    with _Launch("transpose_add", x, 4.0 * x.numel() + (2.0 * x.numel() if residual is not None else 0.0)):
+        rc = load_library().cgs_transpose_add_fwd(x.data_ptr(), r_ptr, out.data_ptr(), n, r, c, _stream(x))
+    _check(rc, "cgs_transpose_add_fwd")
+    return out
 
 
 # ----------------------------------------------------------------------------------------------

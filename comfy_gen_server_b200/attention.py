@@ -319,6 +319,25 @@ class BasicTransformerBlock(nn.Module):
 # ----------------------------------------------------------------------------------------------
 # spatial transformer
 # ----------------------------------------------------------------------------------------------
+def _fast_layout(x) -> bool:
+    return x.is_cuda and x.dtype == torch.bfloat16 and x.is_contiguous()
+
+
+def _to_tokens(x):
+    """'b c h w -> b (h w) c' (attention.py:628)."""
+    b, c, h, w = x.shape
+    if _fast_layout(x) and c % 8 == 0 and (h * w) % 8 == 0:
+        return _native.transpose_add(x.view(b, c, h * w))
+    return x.permute(0, 2, 3, 1).reshape(b, h * w, c).contiguous()
+
+
+def _to_image(x, h, w, residual):
+    """'b (h w) c -> b c h w' (attention.py:636), plus the `+ x_in` of attention.py:639 when `residual` is given."""
+    b, n, c = x.shape
+    if _fast_layout(x) and c % 8 == 0 and n % 8 == 0 and (residual is None or _fast_layout(residual)):
+        return _native.transpose_add(x, residual).view(b, c, h, w)
+    x = x.reshape(b, h, w, c).permute(0, 3, 1, 2).contiguous()
+    return x if residual is None else x + residual
 class SpatialTransformer(nn.Module):
     """attention.py:577-639: GroupNorm(32, eps 1e-6) -> proj_in -> tokens -> blocks -> proj_out -> image, + x_in."""
     def __init__(self, in_channels, n_heads, d_head, depth=1, dropout=0., context_dim=None, disable_self_attn=False,
@@ -354,7 +373,7 @@ class SpatialTransformer(nn.Module):
         x = self.norm(x)
         if not self.use_linear:
             x = self.proj_in(x)
-        x = x.permute(0, 2, 3, 1).reshape(b, h * w, -1).contiguous()
+        x = _to_tokens(x)
         if self.use_linear:
             x = self.proj_in(x)
         for i, block in enumerate(self.transformer_blocks):
@@ -362,7 +381,7 @@ class SpatialTransformer(nn.Module):
             x = block(x, context=context[i], transformer_options=transformer_options)
         if self.use_linear:
             x = self.proj_out(x)
-        x = x.reshape(b, h, w, -1).permute(0, 3, 1, 2).contiguous()
-        if not self.use_linear:
-            x = self.proj_out(x)
+            return _to_image(x, h, w, x_in)            # layout change and `+ x_in` in one kernel
+        x = _to_image(x, h, w, None)
+        x = self.proj_out(x)
         return x + x_in

@@ -16,7 +16,7 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libcgs_b200.so")
 STAMP_PATH = os.path.join(PKG_DIR, ".libcgs_b200.stamp")
 
-SOURCES = ["common.cu", "layernorm.cu", "sampler_tail.cu", "geglu_gemm.cu", "attention.cu", "groupnorm.cu"]
+SOURCES = ["common.cu", "layernorm.cu", "sampler_tail.cu", "geglu_gemm.cu", "attention.cu", "groupnorm.cu", "transpose.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -17,9 +17,9 @@ struct alignas(16) GN8 {
 
 template <bool SILU>
 __global__ void __launch_bounds__(512)
-groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
-                 const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y, int C, int HW, int groups,
-                 float eps) {
+groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ add_nc,
+                 const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
+                 __nv_bfloat16* __restrict__ y, int C, int HW, int groups, float eps) {
     const int g = blockIdx.x, n = blockIdx.y;
     const int cpg = C / groups;
     const long long len = (long long)cpg * HW;
@@ -27,9 +27,18 @@ groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __res
     const GN8* xv = reinterpret_cast<const GN8*>(x + base);
     const int nvec = (int)(len >> 3);
 
+    const int vec_per_ch = HW >> 3;
+    // optional per-(sample, channel) addend: the ResBlock's `h + emb_out[..., None, None]` (openaimodel.py:259),
+    // added in bf16 like the reference, without a separate pass over h
+    const __nv_bfloat16* add_n = add_nc != nullptr ? add_nc + (size_t)n * C + g * cpg : nullptr;
     float s = 0.f, ss = 0.f;
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        const GN8 a = xv[i];
+        GN8 a = xv[i];
+        if (add_n != nullptr) {
+            const __nv_bfloat162 e2 = __bfloat162bfloat162(add_n[i / vec_per_ch]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a.v[j] = __hadd2_rn(a.v[j], e2);
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const float2 f = __bfloat1622float2(a.v[j]);
@@ -66,12 +75,16 @@ groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __res
     const float mean = stats[0], rstd = stats[1];
 
     GN8* yv = reinterpret_cast<GN8*>(y + base);
-    const int vec_per_ch = HW >> 3;
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
         const int c = g * cpg + i / vec_per_ch;
         const float ga = __bfloat162float(gamma[c]) * rstd;
         const float be = __bfloat162float(beta[c]) - mean * ga;
-        const GN8 a = xv[i];          // second read: L2-resident
+        GN8 a = xv[i];          // second read: L2-resident
+        if (add_n != nullptr) {
+            const __nv_bfloat162 e2 = __bfloat162bfloat162(add_n[i / vec_per_ch]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a.v[j] = __hadd2_rn(a.v[j], e2);
+        }
         GN8 o;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -89,8 +102,8 @@ groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __res
 
 }  // namespace cgs
 
-extern "C" int cgs_groupnorm_fwd(const void* x, const void* gamma, const void* beta, void* y, int N, int C, int HW,
-                                 int groups, float eps, int silu, void* stream) {
+extern "C" int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
+                                 int N, int C, int HW, int groups, float eps, int silu, void* stream) {
     using namespace cgs;
     if (N < 0 || C <= 0 || HW <= 0 || groups <= 0 || C % groups != 0) {
         set_last_error("groupnorm: bad sizes N=%d C=%d HW=%d groups=%d", N, C, HW, groups);
@@ -107,14 +120,15 @@ extern "C" int cgs_groupnorm_fwd(const void* x, const void* gamma, const void* b
     }
     dim3 grid(groups, N);
     auto xp = static_cast<const __nv_bfloat16*>(x);
+    auto ap = static_cast<const __nv_bfloat16*>(add_nc);
     auto gp = static_cast<const __nv_bfloat16*>(gamma);
     auto bp = static_cast<const __nv_bfloat16*>(beta);
     auto yp = static_cast<__nv_bfloat16*>(y);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (silu)
-        groupnorm_kernel<true><<<grid, 512, 0, st>>>(xp, gp, bp, yp, C, HW, groups, eps);
+        groupnorm_kernel<true><<<grid, 512, 0, st>>>(xp, ap, gp, bp, yp, C, HW, groups, eps);
     else
-        groupnorm_kernel<false><<<grid, 512, 0, st>>>(xp, gp, bp, yp, C, HW, groups, eps);
+        groupnorm_kernel<false><<<grid, 512, 0, st>>>(xp, ap, gp, bp, yp, C, HW, groups, eps);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }

@@ -1,0 +1,87 @@
+// Layout change at the edges of a SpatialTransformer: NCHW <-> token-major, optionally fused with
+// the residual add that follows it.
+//     out[n, c, r] = in[n, r, c] (+ residual[n, c, r])          in [N, R, C], out / residual [N, C, R], bf16
+// Replaces `rearrange(x, 'b c h w -> b (h w) c').contiguous()` (in = NCHW viewed as [N, C, HW], no residual) and
+// `rearrange(x, 'b (h w) c -> b c h w').contiguous()` + `x + x_in`
+// (reference comfy/ldm/modules/attention.py:628, 636, 639). ATen runs the permuted copy as a non-vectorised
+// strided kernel (0.13 ms for 42 MB, 0.66 TB/s); this is a 64 x 64 shared-memory tile transpose with 16-byte global
+// accesses on both sides. HBM-bound: algorithmic bytes = 2 * N*R*C * 2 (+ residual read).
+#include "common.cuh"
+
+namespace cgs {
+
+constexpr int TT = 64;
+
+__global__ void __launch_bounds__(256)
+transpose_add_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ residual,
+                     __nv_bfloat16* __restrict__ out, int R, int C) {
+    __shared__ __align__(16) unsigned short tile[TT][TT + 2];   // +2 halves: row stride 33 words, conflict-free columns
+    const int n = blockIdx.z;
+    const int r0 = blockIdx.y * TT, c0 = blockIdx.x * TT;
+    const unsigned short* src = reinterpret_cast<const unsigned short*>(in) + (size_t)n * R * C;
+    const int chunk = (threadIdx.x & 7) * 8, lrow = threadIdx.x >> 3;   // 8 x 16-byte chunks per 64-wide row, 32 rows per pass
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int r = r0 + lrow + 32 * i, c = c0 + chunk;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (r < R && c < C) v = *reinterpret_cast<const uint4*>(src + (size_t)r * C + c);
+        unsigned short* t = &tile[lrow + 32 * i][chunk];
+        *reinterpret_cast<uint32_t*>(t + 0) = v.x;
+        *reinterpret_cast<uint32_t*>(t + 2) = v.y;
+        *reinterpret_cast<uint32_t*>(t + 4) = v.z;
+        *reinterpret_cast<uint32_t*>(t + 6) = v.w;
+    }
+    __syncthreads();
+    unsigned short* dst = reinterpret_cast<unsigned short*>(out) + (size_t)n * R * C;
+    const unsigned short* res = reinterpret_cast<const unsigned short*>(residual);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int cc = lrow + 32 * i;           // output row inside the tile = input column
+        const int c = c0 + cc, r = r0 + chunk;  // 8 consecutive output columns = input rows r .. r+7
+        if (c < C && r < R) {
+            unsigned short e[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) e[k] = tile[chunk + k][cc];
+            uint4 v;
+            v.x = e[0] | (uint32_t(e[1]) << 16);
+            v.y = e[2] | (uint32_t(e[3]) << 16);
+            v.z = e[4] | (uint32_t(e[5]) << 16);
+            v.w = e[6] | (uint32_t(e[7]) << 16);
+            const size_t o = (size_t)n * R * C + (size_t)c * R + r;
+            if (res != nullptr) {
+                const uint4 rv = *reinterpret_cast<const uint4*>(res + o);
+                __nv_bfloat162* a = reinterpret_cast<__nv_bfloat162*>(&v);
+                const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&rv);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) a[k] = __hadd2_rn(a[k], b[k]);   // bf16 add, as the reference's x + x_in
+            }
+            *reinterpret_cast<uint4*>(dst + (size_t)c * R + r) = v;
+        }
+    }
+}
+
+}  // namespace cgs
+
+extern "C" int cgs_transpose_add_fwd(const void* in, const void* residual, void* out, int N, int R, int C,
+                                     void* stream) {
+    using namespace cgs;
+    if (N < 0 || R <= 0 || C <= 0) {
+        set_last_error("transpose_add: bad sizes N=%d R=%d C=%d", N, R, C);
+        return kBadArgument;
+    }
+    if (N == 0) return kOk;
+    if (R % 8 != 0 || C % 8 != 0) {
+        set_last_error("transpose_add: R=%d and C=%d must be multiples of 8", R, C);
+        return kUnsupportedShape;
+    }
+    if (N > 65535 || (R + TT - 1) / TT > 65535) {
+        set_last_error("transpose_add: N=%d / R=%d exceed the grid limits", N, R);
+        return kUnsupportedShape;
+    }
+    dim3 grid((C + TT - 1) / TT, (R + TT - 1) / TT, N);
+    transpose_add_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(in), static_cast<const __nv_bfloat16*>(residual),
+        static_cast<__nv_bfloat16*>(out), R, C);
+    CGS_CUDA_CHECK(cudaGetLastError());
+    return kOk;
+}

@@ -121,7 +121,7 @@ class b200_ops:
             return (_native_ok(input) and input.dim() == 4 and input.is_contiguous() and self.affine
                     and (input.shape[2] * input.shape[3]) % 8 == 0)
 
-        def forward_fused(self, input, silu=False):
+        def forward_fused(self, input, silu=False, add_nc=None):
             """GroupNorm with the SiLU that follows it in a ResBlock fused in (cgs_groupnorm_fwd) when the tensor
             is a contiguous NCHW bf16 CUDA tensor; otherwise the reference's F.group_norm (+ F.silu) library path,
             which is what the reference runs for this op."""
@@ -130,7 +130,9 @@ class b200_ops:
             else:
                 weight, bias = self.weight, self.bias
             if self.native_ok(input) and weight.dtype == torch.bfloat16:
-                return _native.group_norm(input, weight, bias, self.num_groups, self.eps, silu)
+                return _native.group_norm(input, weight, bias, self.num_groups, self.eps, silu, add_nc)
+            if add_nc is not None:
+                input = input + add_nc[..., None, None]
             out = torch.nn.functional.group_norm(input, self.num_groups, weight, bias, self.eps)
             return torch.nn.functional.silu(out) if silu else out
 

@@ -36,12 +36,15 @@ class TimestepBlock(nn.Module):
     pass
 
 
-def _norm_silu(norm, x):
+def _norm_silu(norm, x, add_nc=None):
     """GroupNorm -> SiLU (the first two layers of ResBlock.in_layers / out_layers and of UNetModel.out), fused
-    into one kernel when the norm is the B200 operator class."""
+    into one kernel when the norm is the B200 operator class. `add_nc` [N, C]: the timestep embedding that the
+    ResBlock adds to h right before out_layers, folded into the same kernel."""
     fused = getattr(norm, "forward_fused", None)
     if fused is not None:
-        return fused(x, True)
+        return fused(x, True, add_nc)
+    if add_nc is not None:
+        x = x + add_nc[..., None, None]
     return F.silu(norm(x))
 
 
@@ -107,8 +110,7 @@ class ResBlock(TimestepBlock):
     def forward(self, x, emb):
         h = self.in_layers[2](_norm_silu(self.in_layers[0], x))
         emb_out = self.emb_layers(emb).type(h.dtype)
-        h = h + emb_out[..., None, None]
-        h = self.out_layers[3](self.out_layers[2](_norm_silu(self.out_layers[0], h)))
+        h = self.out_layers[3](self.out_layers[2](_norm_silu(self.out_layers[0], h, emb_out.contiguous())))
         return self.skip_connection(x) + h
 
 

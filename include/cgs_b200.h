@@ -78,9 +78,19 @@ int cgs_add_layernorm_fwd(const void* x, const void* residual, const void* gamma
  * (comfy/ldm/modules/diffusionmodules/openaimodel.py:177-181, 213-217, 805-807), and SpatialTransformer.norm
  * (comfy/ldm/modules/attention.py:595; silu = 0, eps = 1e-6).
  *   x, y [N, C, H*W] bf16 contiguous; gamma, beta [C] bf16; C % groups == 0; H*W % 8 == 0; fp32 statistics.
+ *   add_nc [N, C] bf16 or NULL: a per-(sample, channel) addend applied (in bf16) before the norm -- the ResBlock's
+ *   `h + emb_out[..., None, None]` (openaimodel.py:255-259) without a separate pass over h.
  */
-int cgs_groupnorm_fwd(const void* x, const void* gamma, const void* beta, void* y,
+int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
                       int N, int C, int HW, int groups, float eps, int silu, void* stream);
+
+/*
+ * Batched 2-D transpose with an optional residual add: out[n, c, r] = in[n, r, c] (+ residual[n, c, r]).
+ * Replaces the NCHW <-> token-major rearranges at the edges of SpatialTransformer.forward and the `x + x_in` that
+ * follows the second one (comfy/ldm/modules/attention.py:628, 636, 639).
+ *   in [N, R, C], out / residual [N, C, R] bf16 contiguous; R, C multiples of 8; out must not alias in.
+ */
+int cgs_transpose_add_fwd(const void* in, const void* residual, void* out, int N, int R, int C, void* stream);
 
 /*
  * GEGLU projection (G1): y[m, n] = (x W^T + b)[m, n] * gelu_erf((x W^T + b)[m, N + n]).

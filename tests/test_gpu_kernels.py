@@ -155,6 +155,25 @@ def test_groupnorm_silu_vs_oracle(N_, C, H, W, silu):
     assert (y - ref).abs().max() <= ulp_tol(ref)
 
 
+def test_groupnorm_with_channel_addend():
+    """ResBlock form: GroupNorm(h + emb[:, :, None, None]) -> SiLU, the add done in bf16 like the reference."""
+    x = bf(randn((2, 320, 16, 16), 1, 2.0))
+    e = bf(randn((2, 320), 4))
+    w, b = bf(randn((320,), 2) * 0.2 + 1), bf(randn((320,), 3) * 0.2)
+    y = N().group_norm(x, w, b, 32, 1e-5, True, e).float().cpu()
+    h = (x + e[..., None, None]).float().cpu()
+    ref = torch.nn.functional.silu(torch.nn.functional.group_norm(h, 32, w.float().cpu(), b.float().cpu(), 1e-5))
+    assert (y - ref).abs().max() <= ulp_tol(ref)
+
+
+@pytest.mark.parametrize("N_,R,C", [(2, 4096, 640), (2, 1024, 1280), (3, 144, 1280), (1, 8, 8), (2, 576, 320), (1, 72, 200)])
+def test_transpose_add_exact(N_, R, C):
+    x = bf(randn((N_, R, C), 1))
+    r = bf(randn((N_, C, R), 2))
+    assert torch.equal(N().transpose_add(x), x.transpose(1, 2).contiguous())
+    assert torch.equal(N().transpose_add(x, r), x.transpose(1, 2).contiguous() + r)
+
+
 def test_groupnorm_errors():
     n = N()
     w = bf(torch.ones(64))
