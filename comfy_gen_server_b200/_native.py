@@ -26,6 +26,7 @@ _SIGNATURES = {
     "cgs_layernorm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_add_layernorm_fwd": [_c_void_p] * 6 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
+    "cgs_groupnorm_nhwc_fwd": [_c_void_p] * 6 + [_c_ll] + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
@@ -38,7 +39,7 @@ _SIGNATURES = {
                                                    _c_int] + [_c_float] * 4 + [_c_void_p, _c_void_p,
                                                                                _c_ll, _c_ll, _c_void_p],
 }
-EXPORTED_SYMBOLS = ["cgs_last_error", "cgs_abi_version", *_SIGNATURES.keys()]
+EXPORTED_SYMBOLS = ["cgs_last_error", "cgs_abi_version", "cgs_groupnorm_nhwc_scratch_bytes", *_SIGNATURES.keys()]
 
 _lib = None
 _lib_lock = threading.Lock()
@@ -66,6 +67,8 @@ def load_library(path: Optional[str] = None) -> ctypes.CDLL:
         lib.cgs_last_error.argtypes = []
         lib.cgs_abi_version.restype = _c_int
         lib.cgs_abi_version.argtypes = []
+        lib.cgs_groupnorm_nhwc_scratch_bytes.restype = _c_ll
+        lib.cgs_groupnorm_nhwc_scratch_bytes.argtypes = [_c_int] * 4
         for name, argtypes in _SIGNATURES.items():
             fn = getattr(lib, name)
             fn.restype = _c_int
@@ -104,13 +107,13 @@ def timed_family_totals():
 
 class _Launch:
     """with _Launch('attention', stream_tensor, work): rc = lib.fn(...)"""
-    __slots__ = ("family", "t", "work", "ev")
+    __slots__ = ("family", "t", "work", "ev", "n")
 
-    def __init__(self, family, t, work=0.0):
-        self.family, self.t, self.work, self.ev = family, t, work, None
+    def __init__(self, family, t, work=0.0, n=1):
+        self.family, self.t, self.work, self.ev, self.n = family, t, work, None, n
 
     def __enter__(self):
-        LAUNCHES[self.family] = LAUNCHES.get(self.family, 0) + 1
+        LAUNCHES[self.family] = LAUNCHES.get(self.family, 0) + self.n
         if _timed_family == self.family:
             self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             self.ev[0].record(torch.cuda.current_stream(self.t.device))
@@ -215,9 +218,13 @@ def group_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, groups
     _require_cuda("group_norm x", x, torch.bfloat16)
     _require_cuda("group_norm weight", weight, torch.bfloat16)
     _require_cuda("group_norm bias", bias, torch.bfloat16)
-    if x.dim() != 4 or not x.is_contiguous():
-        raise RuntimeError("group_norm: expected a contiguous [N, C, H, W] tensor")
+    if x.dim() != 4:
+        raise RuntimeError("group_norm: expected a 4-D [N, C, H, W] tensor")
     n, c, h, w = x.shape
+    if not x.is_contiguous():
+        if x.is_contiguous(memory_format=torch.channels_last):
+            return _group_norm_nhwc(x, weight, bias, groups, eps, silu, add_nc)
+        raise RuntimeError("group_norm: expected a contiguous (NCHW) or channels_last (NHWC) tensor")
     a_ptr = None
     if add_nc is not None:
         _require_cuda("group_norm add_nc", add_nc, torch.bfloat16)
@@ -229,6 +236,33 @@ def group_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, groups
         rc = load_library().cgs_groupnorm_fwd(x.data_ptr(), a_ptr, weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
                                               n, c, h * w, groups, eps, int(silu), _stream(x))
     _check(rc, "cgs_groupnorm_fwd")
+    return y
+
+
+_gn_scratch: dict = {}
+
+
+def _group_norm_nhwc(x, weight, bias, groups, eps, silu, add_nc):
+    """channels_last input -> channels_last output; the partial-statistics scratch buffer is cached per device
+    (calls on one stream are ordered, so consecutive calls may share it)."""
+    n, c, h, w = x.shape
+    a_ptr = None
+    if add_nc is not None:
+        _require_cuda("group_norm add_nc", add_nc, torch.bfloat16)
+        if add_nc.shape != (n, c) or not add_nc.is_contiguous():
+            raise RuntimeError("group_norm: add_nc must be a contiguous [N, C] tensor")
+        a_ptr = add_nc.data_ptr()
+    lib = load_library()
+    need = lib.cgs_groupnorm_nhwc_scratch_bytes(n, c, h * w, groups)
+    key = (x.device, torch.cuda.current_stream(x.device).cuda_stream)
+    buf = _gn_scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = _gn_scratch[key] = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
+    y = torch.empty_like(x)          # preserves channels_last
+    with _Launch("groupnorm_nhwc", x, 6.0 * x.numel(), n=2):
+        rc = lib.cgs_groupnorm_nhwc_fwd(x.data_ptr(), a_ptr, weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+                                        buf.data_ptr(), buf.numel(), n, c, h * w, groups, eps, int(silu), _stream(x))
+    _check(rc, "cgs_groupnorm_nhwc_fwd")
     return y
 
 

@@ -323,9 +323,15 @@ def _fast_layout(x) -> bool:
     return x.is_cuda and x.dtype == torch.bfloat16 and x.is_contiguous()
 
 
+def _is_channels_last(x) -> bool:
+    return x.dim() == 4 and not x.is_contiguous() and x.is_contiguous(memory_format=torch.channels_last)
+
+
 def _to_tokens(x):
-    """'b c h w -> b (h w) c' (attention.py:628)."""
+    """'b c h w -> b (h w) c' (attention.py:628). Free for channels_last activations: NHWC *is* token-major."""
     b, c, h, w = x.shape
+    if _is_channels_last(x):
+        return x.permute(0, 2, 3, 1).reshape(b, h * w, c)
     if _fast_layout(x) and c % 8 == 0 and (h * w) % 8 == 0:
         return _native.transpose_add(x.view(b, c, h * w))
     return x.permute(0, 2, 3, 1).reshape(b, h * w, c).contiguous()
@@ -334,6 +340,9 @@ def _to_tokens(x):
 def _to_image(x, h, w, residual):
     """'b (h w) c -> b c h w' (attention.py:636), plus the `+ x_in` of attention.py:639 when `residual` is given."""
     b, n, c = x.shape
+    if residual is not None and _is_channels_last(residual) and x.is_contiguous():
+        # channels_last pipeline: the token tensor already is the NHWC image; the add stays a plain vectorised add
+        return x.view(b, h, w, c).permute(0, 3, 1, 2) + residual
     if _fast_layout(x) and c % 8 == 0 and n % 8 == 0 and (residual is None or _fast_layout(residual)):
         return _native.transpose_add(x, residual).view(b, c, h, w)
     x = x.reshape(b, h, w, c).permute(0, 3, 1, 2).contiguous()
@@ -382,6 +391,9 @@ class SpatialTransformer(nn.Module):
         if self.use_linear:
             x = self.proj_out(x)
             return _to_image(x, h, w, x_in)            # layout change and `+ x_in` in one kernel
-        x = _to_image(x, h, w, None)
+        if _is_channels_last(x_in) and x.is_contiguous():
+            x = x.view(b, h, w, -1).permute(0, 3, 1, 2)         # NHWC view, no copy
+        else:
+            x = _to_image(x, h, w, None)
         x = self.proj_out(x)
         return x + x_in

@@ -100,6 +100,171 @@ groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __res
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Channels-last (NHWC) form: x, y [N, H*W, C]. Keeping the UNet's activations NHWC end to end removes
+// cuDNN's per-convolution NCHW<->NHWC conversion kernels and makes the SpatialTransformer's token layout free.
+// A group's channels are now only cpg (10..80) contiguous elements per pixel, so the work is split by pixel rows,
+// not by group:
+//   kernel 1  every CTA reduces a chunk of pixel rows for ALL 32 groups -> partial (sum, sum of squares) per
+//             (sample, chunk, group) in a small global scratch buffer;
+//   kernel 2  every CTA first adds up its sample's partials (L2-resident, a few KB), then normalises its chunk.
+// Thread <-> channel mapping is fixed (a thread always owns the same 8 channels), so gamma/beta/group ids live in
+// registers; a vector of 8 channels straddles at most two groups (cpg >= 8).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kGnMaxGroups = 32;
+
+struct GnNhwcGeom {
+    int nvec;           // C / 8
+    int rows_per_iter;  // pixel rows handled per block iteration
+    int threads;        // nvec * rows_per_iter
+    int chunks;         // CTAs per sample
+    int rows_per_chunk;
+};
+
+static GnNhwcGeom gn_nhwc_geom(int N, int C, int HW) {
+    GnNhwcGeom g;
+    g.nvec = C / 8;
+    g.rows_per_iter = g.nvec >= 256 ? 1 : 256 / g.nvec;
+    g.threads = g.nvec * g.rows_per_iter;
+    // enough CTAs to fill the GPU a few times over, but no more than 128 partials per sample
+    int want = (sm_count() * 4 + N - 1) / (N > 0 ? N : 1);
+    if (want > 128) want = 128;
+    if (want < 1) want = 1;
+    int rows = (HW + want - 1) / want;
+    rows = ((rows + g.rows_per_iter - 1) / g.rows_per_iter) * g.rows_per_iter;
+    g.rows_per_chunk = rows;
+    g.chunks = (HW + rows - 1) / rows;
+    return g;
+}
+
+__device__ __forceinline__ void gn_load_row_vec(const __nv_bfloat16* xp, const __nv_bfloat162 (&e)[4], bool has_add,
+                                                float (&f)[8]) {
+    GN8 a = *reinterpret_cast<const GN8*>(xp);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (has_add) a.v[j] = __hadd2_rn(a.v[j], e[j]);      // bf16 add, as the reference's h + emb
+        const float2 t = __bfloat1622float2(a.v[j]);
+        f[2 * j] = t.x;
+        f[2 * j + 1] = t.y;
+    }
+}
+
+__global__ void __launch_bounds__(320)
+gn_nhwc_stats_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ add_nc,
+                     float* __restrict__ partial, int C, int HW, int groups, int nvec, int rows_per_iter,
+                     int rows_per_chunk) {
+    __shared__ float acc[kGnMaxGroups][2];
+    const int n = blockIdx.y, chunk = blockIdx.x;
+    const int vec = threadIdx.x % nvec, rsub = threadIdx.x / nvec;
+    const int cpg = C / groups;
+    const int c0 = vec * 8;
+    const int g0 = c0 / cpg;
+    const int split = min(8, (g0 + 1) * cpg - c0);     // channels [0, split) of this vector belong to g0
+    if (threadIdx.x < groups) { acc[threadIdx.x][0] = 0.f; acc[threadIdx.x][1] = 0.f; }
+    __nv_bfloat162 e[4];
+    const bool has_add = add_nc != nullptr;
+    if (has_add) {
+        const GN8 ev = *reinterpret_cast<const GN8*>(add_nc + (size_t)n * C + c0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) e[j] = ev.v[j];
+    }
+    __syncthreads();
+    float sa = 0.f, qa = 0.f, sb = 0.f, qb = 0.f;
+    const int r_begin = chunk * rows_per_chunk;
+    const int r_end = min(HW, r_begin + rows_per_chunk);
+    for (int r = r_begin + rsub; r < r_end; r += rows_per_iter) {
+        float f[8];
+        gn_load_row_vec(x + ((size_t)n * HW + r) * C + c0, e, has_add, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (j < split) { sa += f[j]; qa += f[j] * f[j]; }
+            else           { sb += f[j]; qb += f[j] * f[j]; }
+        }
+    }
+    atomicAdd(&acc[g0][0], sa);
+    atomicAdd(&acc[g0][1], qa);
+    if (split < 8) {
+        atomicAdd(&acc[g0 + 1][0], sb);
+        atomicAdd(&acc[g0 + 1][1], qb);
+    }
+    __syncthreads();
+    if (threadIdx.x < groups) {
+        float* dst = partial + (((size_t)n * gridDim.x + chunk) * groups + threadIdx.x) * 2;
+        dst[0] = acc[threadIdx.x][0];
+        dst[1] = acc[threadIdx.x][1];
+    }
+}
+
+template <bool SILU>
+__global__ void __launch_bounds__(320)
+gn_nhwc_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ add_nc,
+                     const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
+                     const float* __restrict__ partial, __nv_bfloat16* __restrict__ y, int C, int HW, int groups,
+                     int nvec, int rows_per_iter, int rows_per_chunk, float eps) {
+    __shared__ float stat[kGnMaxGroups][2];    // mean, rstd
+    const int n = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x;
+    const int cpg = C / groups;
+    if (threadIdx.x < groups) {
+        float s = 0.f, q = 0.f;
+        const float* src = partial + ((size_t)n * chunks * groups + threadIdx.x) * 2;
+        for (int k = 0; k < chunks; ++k) {
+            s += src[(size_t)k * groups * 2];
+            q += src[(size_t)k * groups * 2 + 1];
+        }
+        const float cnt = (float)cpg * (float)HW;
+        const float mean = s / cnt;
+        const float var = fmaxf(q / cnt - mean * mean, 0.f);
+        stat[threadIdx.x][0] = mean;
+        stat[threadIdx.x][1] = rsqrtf(var + eps);
+    }
+    __syncthreads();
+    const int vec = threadIdx.x % nvec, rsub = threadIdx.x / nvec;
+    const int c0 = vec * 8;
+    const int g0 = c0 / cpg;
+    const int split = min(8, (g0 + 1) * cpg - c0);
+    float ga[8], be[8];
+    {
+        const GN8 gv = *reinterpret_cast<const GN8*>(gamma + c0);
+        const GN8 bv = *reinterpret_cast<const GN8*>(beta + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int g = j < split ? g0 : g0 + 1;
+            const float mean = stat[g][0], rstd = stat[g][1];
+            const float gam = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(&gv)[j]);
+            const float bet = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(&bv)[j]);
+            ga[j] = gam * rstd;
+            be[j] = bet - mean * ga[j];
+        }
+    }
+    __nv_bfloat162 e[4];
+    const bool has_add = add_nc != nullptr;
+    if (has_add) {
+        const GN8 ev = *reinterpret_cast<const GN8*>(add_nc + (size_t)n * C + c0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) e[j] = ev.v[j];
+    }
+    const int r_begin = chunk * rows_per_chunk;
+    const int r_end = min(HW, r_begin + rows_per_chunk);
+    for (int r = r_begin + rsub; r < r_end; r += rows_per_iter) {
+        float f[8];
+        const size_t off = ((size_t)n * HW + r) * C + c0;
+        gn_load_row_vec(x + off, e, has_add, f);
+        GN8 o;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float v0 = fmaf(f[2 * j], ga[2 * j], be[2 * j]);
+            float v1 = fmaf(f[2 * j + 1], ga[2 * j + 1], be[2 * j + 1]);
+            if (SILU) {
+                v0 = v0 / (1.f + __expf(-v0));
+                v1 = v1 / (1.f + __expf(-v1));
+            }
+            o.v[j] = __floats2bfloat162_rn(v0, v1);
+        }
+        *reinterpret_cast<GN8*>(y + off) = o;
+    }
+}
+
 }  // namespace cgs
 
 extern "C" int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
@@ -129,6 +294,57 @@ extern "C" int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* 
         groupnorm_kernel<true><<<grid, 512, 0, st>>>(xp, ap, gp, bp, yp, C, HW, groups, eps);
     else
         groupnorm_kernel<false><<<grid, 512, 0, st>>>(xp, ap, gp, bp, yp, C, HW, groups, eps);
+    CGS_CUDA_CHECK(cudaGetLastError());
+    return kOk;
+}
+
+extern "C" long long cgs_groupnorm_nhwc_scratch_bytes(int N, int C, int HW, int groups) {
+    if (N <= 0 || C <= 0 || HW <= 0 || groups <= 0) return 0;
+    const cgs::GnNhwcGeom g = cgs::gn_nhwc_geom(N, C, HW);
+    return (long long)N * g.chunks * groups * 2 * (long long)sizeof(float);
+}
+
+extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
+                                      void* scratch, long long scratch_bytes, int N, int C, int HW, int groups,
+                                      float eps, int silu, void* stream) {
+    using namespace cgs;
+    if (N < 0 || C <= 0 || HW <= 0 || groups <= 0 || C % groups != 0) {
+        set_last_error("groupnorm_nhwc: bad sizes N=%d C=%d HW=%d groups=%d", N, C, HW, groups);
+        return kBadArgument;
+    }
+    if (N == 0) return kOk;
+    if (C % 8 != 0 || C / groups < 8 || groups > kGnMaxGroups || C / 8 > 320) {
+        set_last_error("groupnorm_nhwc: C=%d groups=%d unsupported (C %% 8 == 0, C/groups >= 8, groups <= 32, C <= 2560)",
+                       C, groups);
+        return kUnsupportedShape;
+    }
+    if (N > 65535) {
+        set_last_error("groupnorm_nhwc: N=%d exceeds the grid limit", N);
+        return kUnsupportedShape;
+    }
+    const GnNhwcGeom g = gn_nhwc_geom(N, C, HW);
+    const long long need = (long long)N * g.chunks * groups * 2 * (long long)sizeof(float);
+    if (scratch == nullptr || scratch_bytes < need) {
+        set_last_error("groupnorm_nhwc: scratch buffer of %lld bytes needed (got %lld)", need, scratch_bytes);
+        return kScratchTooSmall;
+    }
+    dim3 grid(g.chunks, N);
+    auto xp = static_cast<const __nv_bfloat16*>(x);
+    auto ap = static_cast<const __nv_bfloat16*>(add_nc);
+    auto gp = static_cast<const __nv_bfloat16*>(gamma);
+    auto bp = static_cast<const __nv_bfloat16*>(beta);
+    auto yp = static_cast<__nv_bfloat16*>(y);
+    auto sp = static_cast<float*>(scratch);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    gn_nhwc_stats_kernel<<<grid, g.threads, 0, st>>>(xp, ap, sp, C, HW, groups, g.nvec, g.rows_per_iter,
+                                                     g.rows_per_chunk);
+    CGS_CUDA_CHECK(cudaGetLastError());
+    if (silu)
+        gn_nhwc_apply_kernel<true><<<grid, g.threads, 0, st>>>(xp, ap, gp, bp, sp, yp, C, HW, groups, g.nvec,
+                                                               g.rows_per_iter, g.rows_per_chunk, eps);
+    else
+        gn_nhwc_apply_kernel<false><<<grid, g.threads, 0, st>>>(xp, ap, gp, bp, sp, yp, C, HW, groups, g.nvec,
+                                                                g.rows_per_iter, g.rows_per_chunk, eps);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }

@@ -41,6 +41,18 @@ class BaseModel(torch.nn.Module):
         self.model_sampling = model_sampling(prediction)
         self.adm_channels = self.unet_config.get("adm_in_channels", None) or 0
         self.concat_keys = ()
+        self.channels_last = False    # set by use_channels_last(): activations NHWC end to end
+
+    def use_channels_last(self, enable=True):
+        """Keep the UNet's activations (and conv weights) in torch.channels_last: cuDNN then runs its NHWC kernels
+        without per-convolution layout conversions, GroupNorm uses the NHWC kernels and the SpatialTransformer's
+        image <-> token rearranges become views. Requires every GroupNorm to have >= 8 channels per group."""
+        self.channels_last = bool(enable)
+        fmt = torch.channels_last if enable else torch.contiguous_format
+        for p in self.diffusion_model.parameters():
+            if p.dim() == 4:
+                p.data = p.data.contiguous(memory_format=fmt)
+        return self
 
     # -- reference semantics -------------------------------------------------------------------
     def apply_model(self, x, t, c_concat=None, c_crossattn=None, control=None, transformer_options={}, **kwargs):
@@ -54,6 +66,8 @@ class BaseModel(torch.nn.Module):
             if c_concat is not None:
                 xc = torch.cat([xc] + [c_concat], dim=1)
             xc = xc.to(dtype)
+        if self.channels_last:
+            xc = xc.contiguous(memory_format=torch.channels_last)
         t = self.model_sampling.timestep(t).float()
         context = c_crossattn.to(dtype)
         extra_conds = {}
@@ -75,6 +89,8 @@ class BaseModel(torch.nn.Module):
     def unet_raw(self, xc, timesteps, context, y=None, transformer_options=None):
         """Raw UNet output (eps or v) for an already scaled / cast input batch."""
         kw = {} if y is None else {"y": y}
+        if self.channels_last:
+            xc = xc.contiguous(memory_format=torch.channels_last)
         return self.diffusion_model(xc, timesteps, context=context,
                                     transformer_options={} if transformer_options is None else transformer_options,
                                     **kw)
@@ -128,7 +144,7 @@ class SDXL(BaseModel):
         return torch.cat((clip_pooled.to(flat.device), flat), dim=1)
 
 
-def build_model(family: str, dtype=torch.bfloat16, device=None, state_dict=None, seed=None):
+def build_model(family: str, dtype=torch.bfloat16, device=None, state_dict=None, seed=None, channels_last=None):
     """Construct one of the BASELINE.json model families ('sd15', 'sd21v', 'sdxl', 'tiny_*') and load either
     a given UNet state dict or seeded random weights (there are no checkpoints in this setting)."""
     fam = uc.FAMILIES[family]
@@ -150,4 +166,8 @@ def build_model(family: str, dtype=torch.bfloat16, device=None, state_dict=None,
     else:
         model.diffusion_model.load_state_dict({k: v.to(dtype) for k, v in state_dict.items()})
     model.model_sampling.to("cpu")
+    if channels_last is None:      # auto: every GroupNorm needs >= 8 channels per group (model_channels >= 256)
+        channels_last = fam["unet"]["model_channels"] // 32 >= 8 and torch.device(device or "cpu").type == "cuda"
+    if channels_last:
+        model.use_channels_last(True)
     return model.eval()

@@ -118,8 +118,14 @@ class b200_ops:
             return None
 
         def native_ok(self, input):
-            return (_native_ok(input) and input.dim() == 4 and input.is_contiguous() and self.affine
-                    and (input.shape[2] * input.shape[3]) % 8 == 0)
+            if not (_native_ok(input) and input.dim() == 4 and self.affine):
+                return False
+            c = input.shape[1]
+            if input.is_contiguous():                                       # NCHW kernel
+                return (input.shape[2] * input.shape[3]) % 8 == 0
+            if input.is_contiguous(memory_format=torch.channels_last):      # NHWC kernels
+                return c % 8 == 0 and c // self.num_groups >= 8 and self.num_groups <= 32 and c <= 2560
+            return False
 
         def forward_fused(self, input, silu=False, add_nc=None):
             """GroupNorm with the SiLU that follows it in a ResBlock fused in (cgs_groupnorm_fwd) when the tensor

@@ -85,6 +85,18 @@ int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* gamma, cons
                       int N, int C, int HW, int groups, float eps, int silu, void* stream);
 
 /*
+ * The same GroupNorm (+ SiLU, + addend) for channels-last activations: x, y [N, H*W, C] bf16 (torch
+ * memory_format=channels_last). Two launches (partial statistics per pixel-row chunk, then normalise) that
+ * communicate through `scratch`, a caller-provided device buffer of at least
+ * cgs_groupnorm_nhwc_scratch_bytes(N, C, HW, groups) bytes; it need not be initialised and may be reused by the next
+ * call on the same stream. C % 8 == 0, C / groups >= 8, groups <= 32, C <= 2560.
+ */
+long long cgs_groupnorm_nhwc_scratch_bytes(int N, int C, int HW, int groups);
+int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
+                           void* scratch, long long scratch_bytes,
+                           int N, int C, int HW, int groups, float eps, int silu, void* stream);
+
+/*
  * Batched 2-D transpose with an optional residual add: out[n, c, r] = in[n, r, c] (+ residual[n, c, r]).
  * Replaces the NCHW <-> token-major rearranges at the edges of SpatialTransformer.forward and the `x + x_in` that
  * follows the second one (comfy/ldm/modules/attention.py:628, 636, 639).

@@ -178,6 +178,30 @@ def test_sampler_cfg_function_hook_and_cfg1():
     assert torch.isfinite(one).all() and cosine(base, one) < 0.9999
 
 
+def test_channels_last_pipeline_matches_nchw_pipeline():
+    """the NHWC end-to-end UNet (channels_last GroupNorm kernels, cuDNN NHWC convs, free token views)
+    gives the same latents as the NCHW pipeline."""
+    from comfy_gen_server_b200 import sample as S
+    from comfy_gen_server_b200.model_base import build_model
+    from comfy_gen_server_b200.model_management import ModelPatcher
+    g = load_golden("e2e_sd15_config1")
+    seed = int(g["seed"])
+    latent = torch.zeros(1, 4, 64, 64)
+    noise = S.prepare_noise(latent, seed)
+    outs = []
+    for cl in (False, True):
+        model = build_model("sd15", dtype=torch.bfloat16, device=DEV, seed=seed, channels_last=cl)
+        assert model.channels_last == cl
+        with torch.inference_mode():
+            outs.append(S.sample(ModelPatcher(model, DEV), noise, 4, 7.0, "euler", "normal", [[g["positive"], {}]],
+                                 [[g["negative"], {}]], latent, seed=seed))
+        del model
+        torch.cuda.empty_cache()
+    c = cosine(outs[0], outs[1])
+    print(f"channels_last vs NCHW pipeline: cosine {c:.6f}")
+    assert c > 0.9995
+
+
 def test_config1_sd15_full_size_vs_reference():
     """BASELINE.json configs[0]: SD1.5 512x512 batch 1, 20-step Euler, CFG 7.0 -- the reference's CPU run
     (fp32, 143.7 s on 8 cores in the build container) vs this path in bf16 on the GPU."""

@@ -166,6 +166,28 @@ def test_groupnorm_with_channel_addend():
     assert (y - ref).abs().max() <= ulp_tol(ref)
 
 
+@pytest.mark.parametrize("N_,C,H,W,silu,add", [(2, 320, 32, 32, True, True), (2, 640, 16, 16, True, False),
+                                               (1, 1280, 8, 8, False, False), (3, 960, 12, 12, True, True),
+                                               (2, 2560, 16, 16, True, False), (1, 256, 3, 5, True, True),
+                                               (2, 1920, 32, 32, True, True)])
+def test_groupnorm_channels_last_vs_oracle(N_, C, H, W, silu, add):
+    x = bf(randn((N_, C, H, W), 1, 2.0) + 0.5).contiguous(memory_format=torch.channels_last)
+    e = bf(randn((N_, C), 4)) if add else None
+    w, b = bf(randn((C,), 2) * 0.2 + 1), bf(randn((C,), 3) * 0.2)
+    eps = 1e-5 if silu else 1e-6
+    y = N().group_norm(x, w, b, 32, eps, silu, e)
+    assert y.is_contiguous(memory_format=torch.channels_last) and y.shape == x.shape
+    h = x if e is None else x + e[..., None, None]
+    ref = torch.nn.functional.group_norm(h.float().cpu(), 32, w.float().cpu(), b.float().cpu(), eps)
+    if silu:
+        ref = torch.nn.functional.silu(ref)
+    assert (y.float().cpu() - ref).abs().max() <= ulp_tol(ref)
+    # same numbers as the NCHW kernel
+    y2 = N().group_norm(x.contiguous(), w, b, 32, eps, silu, e) if (H * W) % 8 == 0 else None
+    if y2 is not None:
+        assert (y.float() - y2.float()).abs().max() <= ulp_tol(ref)
+
+
 @pytest.mark.parametrize("N_,R,C", [(2, 4096, 640), (2, 1024, 1280), (3, 144, 1280), (1, 8, 8), (2, 576, 320), (1, 72, 200)])
 def test_transpose_add_exact(N_, R, C):
     x = bf(randn((N_, R, C), 1))
