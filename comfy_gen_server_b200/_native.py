@@ -27,6 +27,7 @@ _SIGNATURES = {
     "cgs_add_layernorm_fwd": [_c_void_p] * 6 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_fwd": [_c_void_p] * 6 + [_c_ll] + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
+    "cgs_groupnorm_nhwc_noalloc_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],

@@ -348,3 +348,65 @@ extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const v
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the channels-last GroupNorm.
+//
+// cgs_groupnorm_nhwc_fwd needs a scratch buffer that somebody has to cudaMalloc. Some callers cannot: a custom node
+// or serving worker that lives inside the host framework's memory budget (the reference sizes its batches from
+// model_management.get_free_memory(), which cannot see memory taken behind the framework allocator's back), a plain C
+// caller that owns no device allocator at all, or code on a latency path where the device-wide synchronisation of
+// cudaMalloc / cudaFree is not acceptable. For them the partial-statistics buffer lives in the library image itself:
+// a fixed 1 MiB __device__ array that every GPU loading this library carries until the process exits.
+//
+// What the caller has to know:
+//   * the first call on each device looks up the array's device address (cudaGetSymbolAddress) with that device
+//     current -- make that first call during set-up, before any stream capture is started;
+//   * problems whose partial statistics do not fit (N * chunks * groups * 8 bytes > 1 MiB; roughly N > 32 at the
+//     largest feature maps) are refused with CGS_SCRATCH_TOO_SMALL, nothing is launched;
+//   * all calls on a device share the one array and it keeps whatever the previous call left in it. Nothing has to
+//     be zeroed between calls (the statistics kernel overwrites every slot the normalise kernel reads), but two calls
+//     whose kernels overlap on the GPU -- different streams, or different host threads on the same device -- race on
+//     it. Keep them on one stream, or order the streams with events.
+//   * neither this function nor anything it calls allocates or frees memory.
+// ---------------------------------------------------------------------------------------------------------------
+namespace cgs {
+constexpr long long kGnStaticScratchBytes = 1 << 20;
+static __device__ __align__(256) float g_gn_static_scratch[kGnStaticScratchBytes / sizeof(float)];
+// In host code the name above is only a handle for the runtime, not a device address: the address each device
+// assigned to its copy has to be asked for, per device, and is cached here.
+static float* g_gn_static_scratch_addr[64] = {nullptr};
+}  // namespace cgs
+
+extern "C" int cgs_groupnorm_nhwc_noalloc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta,
+                                              void* y, int N, int C, int HW, int groups, float eps, int silu,
+                                              void* stream) {
+    using namespace cgs;
+    int dev = -1;
+    CGS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_last_error("groupnorm_nhwc_noalloc: device ordinal %d not supported (0..63)", dev);
+        return kBadArgument;
+    }
+    if (N > 0 && C > 0 && HW > 0 && groups > 0) {
+        const long long need = cgs_groupnorm_nhwc_scratch_bytes(N, C, HW, groups);
+        if (need > kGnStaticScratchBytes) {
+            set_last_error("groupnorm_nhwc_noalloc: this problem needs %lld bytes of partial statistics but the built-in "
+                           "buffer holds %lld; use cgs_groupnorm_nhwc_fwd with a caller-provided scratch buffer",
+                           need, kGnStaticScratchBytes);
+            return kScratchTooSmall;
+        }
+    }
+    if (g_gn_static_scratch_addr[dev] == nullptr) {
+        // once per device, with that device current (it is: cudaGetDevice above)
+        float* p = nullptr;
+        CGS_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_scratch));
+        if (p == nullptr) {
+            set_last_error("groupnorm_nhwc_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev);
+            return kCudaError;
+        }
+        g_gn_static_scratch_addr[dev] = p;
+    }
+    return cgs_groupnorm_nhwc_fwd(x, add_nc, gamma, beta, y, g_gn_static_scratch_addr[dev], kGnStaticScratchBytes, N, C,
+                                  HW, groups, eps, silu, stream);
+}

@@ -97,6 +97,25 @@ int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma,
                            int N, int C, int HW, int groups, float eps, int silu, void* stream);
 
 /*
+ * cgs_groupnorm_nhwc_fwd for callers that cannot allocate device memory. (No counterpart in the reference: it is
+ * an accommodation of this library's own scratch requirement, not a replacement for a reference call.)
+ * Who needs it: code that gets every byte of device memory from someone else -- a custom node or worker inside the
+ * host framework's memory accounting, a C caller without an allocator -- or that may not pay cudaMalloc's
+ * device-wide synchronisation. The partial-statistics buffer is a fixed 1 MiB array inside the library, present on
+ * every GPU that loads it, for the life of the process.
+ *   - Same arguments and results as cgs_groupnorm_nhwc_fwd, minus the scratch pair.
+ *   - Limit: N * chunks * groups * 8 bytes (= cgs_groupnorm_nhwc_scratch_bytes) must be <= 1 MiB, else
+ *     CGS_SCRATCH_TOO_SMALL and nothing is launched.
+ *   - The first call on a device resolves the array's address on that device; make it during set-up, before any
+ *     stream capture begins.
+ *   - All calls on a device share the array; it is never cleared and need not be, but calls whose kernels overlap
+ *     on the GPU (other streams, other threads) race on it -- serialise them.
+ *   - Allocates and frees nothing.
+ */
+int cgs_groupnorm_nhwc_noalloc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
+                                   int N, int C, int HW, int groups, float eps, int silu, void* stream);
+
+/*
  * Batched 2-D transpose with an optional residual add: out[n, c, r] = in[n, r, c] (+ residual[n, c, r]).
  * Replaces the NCHW <-> token-major rearranges at the edges of SpatialTransformer.forward and the `x + x_in` that
  * follows the second one (comfy/ldm/modules/attention.py:628, 636, 639).
