@@ -154,14 +154,14 @@ __global__ void __launch_bounds__(320)
 gn_nhwc_stats_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ add_nc,
                      float* __restrict__ partial, int C, int HW, int groups, int nvec, int rows_per_iter,
                      int rows_per_chunk) {
-    __shared__ float acc[kGnMaxGroups][2];
+    // per-thread partials, combined in a fixed order (no atomics: results are reproducible run to run)
+    __shared__ float part[320][4];
     const int n = blockIdx.y, chunk = blockIdx.x;
     const int vec = threadIdx.x % nvec, rsub = threadIdx.x / nvec;
     const int cpg = C / groups;
     const int c0 = vec * 8;
     const int g0 = c0 / cpg;
     const int split = min(8, (g0 + 1) * cpg - c0);     // channels [0, split) of this vector belong to g0
-    if (threadIdx.x < groups) { acc[threadIdx.x][0] = 0.f; acc[threadIdx.x][1] = 0.f; }
     __nv_bfloat162 e[4];
     const bool has_add = add_nc != nullptr;
     if (has_add) {
@@ -169,7 +169,6 @@ gn_nhwc_stats_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 #pragma unroll
         for (int j = 0; j < 4; ++j) e[j] = ev.v[j];
     }
-    __syncthreads();
     float sa = 0.f, qa = 0.f, sb = 0.f, qb = 0.f;
     const int r_begin = chunk * rows_per_chunk;
     const int r_end = min(HW, r_begin + rows_per_chunk);
@@ -182,17 +181,28 @@ gn_nhwc_stats_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
             else           { sb += f[j]; qb += f[j] * f[j]; }
         }
     }
-    atomicAdd(&acc[g0][0], sa);
-    atomicAdd(&acc[g0][1], qa);
-    if (split < 8) {
-        atomicAdd(&acc[g0 + 1][0], sb);
-        atomicAdd(&acc[g0 + 1][1], qb);
-    }
+    part[threadIdx.x][0] = sa;
+    part[threadIdx.x][1] = qa;
+    part[threadIdx.x][2] = sb;
+    part[threadIdx.x][3] = qb;
     __syncthreads();
     if (threadIdx.x < groups) {
-        float* dst = partial + (((size_t)n * gridDim.x + chunk) * groups + threadIdx.x) * 2;
-        dst[0] = acc[threadIdx.x][0];
-        dst[1] = acc[threadIdx.x][1];
+        // group g owns channels [g*cpg, (g+1)*cpg): the vectors that touch it, each contributing its "a" half when
+        // the vector starts in g and its "b" half when it started in g-1 and spilled over
+        const int g = threadIdx.x;
+        const int v_first = (g * cpg) / 8, v_last = ((g + 1) * cpg - 1) / 8;
+        float s = 0.f, q = 0.f;
+        for (int v = v_first; v <= v_last; ++v) {
+            const int vg0 = (v * 8) / cpg;                 // group of the vector's first channel
+            for (int rs = 0; rs < rows_per_iter; ++rs) {
+                const float* pp = part[rs * nvec + v];
+                if (vg0 == g) { s += pp[0]; q += pp[1]; }
+                else          { s += pp[2]; q += pp[3]; }  // vg0 == g - 1
+            }
+        }
+        float* dst = partial + (((size_t)n * gridDim.x + chunk) * groups + g) * 2;
+        dst[0] = s;
+        dst[1] = q;
     }
 }
 

@@ -178,6 +178,22 @@ def test_sampler_cfg_function_hook_and_cfg1():
     assert torch.isfinite(one).all() and cosine(base, one) < 0.9999
 
 
+def test_sampling_is_bitwise_reproducible():
+    """Same seed, same weights -> the same latents, bit for bit (no atomics / non-deterministic reductions on the path)."""
+    from comfy_gen_server_b200 import sample as S
+    g = load_golden("e2e_tiny_sdxl_dpmpp2m")
+    seed = int(g["seed"])
+    patcher = _patcher("tiny_sdxl", seed)
+    latent = torch.zeros(2, 4, 16, 16)
+    noise = S.prepare_noise(latent, seed)
+    pos = [[g["positive"], {"pooled_output": g["pooled_pos"]}]]
+    neg = [[g["negative"], {"pooled_output": g["pooled_neg"]}]]
+    with torch.inference_mode():
+        a = S.sample(patcher, noise, 6, 7.0, "dpmpp_2m", "karras", pos, neg, latent, seed=seed)
+        b = S.sample(patcher, noise, 6, 7.0, "dpmpp_2m", "karras", pos, neg, latent, seed=seed)
+    assert torch.equal(a, b)
+
+
 def test_channels_last_pipeline_matches_nchw_pipeline():
     """the NHWC end-to-end UNet (channels_last GroupNorm kernels, cuDNN NHWC convs, free token views)
     gives the same latents as the NCHW pipeline."""

@@ -188,6 +188,14 @@ def test_groupnorm_channels_last_vs_oracle(N_, C, H, W, silu, add):
         assert (y.float() - y2.float()).abs().max() <= ulp_tol(ref)
 
 
+def test_groupnorm_channels_last_is_reproducible():
+    x = bf(randn((4, 640, 64, 64), 1, 2.0)).contiguous(memory_format=torch.channels_last)
+    w, b = bf(randn((640,), 2) * 0.2 + 1), bf(randn((640,), 3) * 0.2)
+    a = N().group_norm(x, w, b, 32, 1e-5, True)
+    for _ in range(3):
+        assert torch.equal(a, N().group_norm(x, w, b, 32, 1e-5, True))
+
+
 @pytest.mark.parametrize("N_,R,C", [(2, 4096, 640), (2, 1024, 1280), (3, 144, 1280), (1, 8, 8), (2, 576, 320), (1, 72, 200)])
 def test_transpose_add_exact(N_, R, C):
     x = bf(randn((N_, R, C), 1))

@@ -51,9 +51,8 @@ def test_noalloc_groupnorm_matches_the_ordinary_entry_point_twice():
                                                 y_new.data_ptr(), n, c, h * w, groups, eps, silu, stream)
         assert rc == 0, lib.cgs_last_error()
         torch.cuda.synchronize()
-        # Same kernels behind both entry points. Their block-level partial sums are combined with shared-memory
-        # float atomics, whose order is not fixed, so two runs may differ in the last bit: the bar is the
-        # library-wide bf16 tolerance (one ulp of the output magnitude), as in tests/test_gpu_kernels.py.
+        # Same kernels behind both entry points; the bar is the library-wide bf16 tolerance (one ulp of the output
+        # magnitude), as in tests/test_gpu_kernels.py.
         tol = float(y_ref.float().abs().max()) * 2 ** -7 + 1e-3
         assert (y_new.float() - y_ref.float()).abs().max() <= tol
         # and against a plain fp32 computation, so that "identical" cannot mean "identically wrong"
