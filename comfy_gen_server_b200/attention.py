@@ -342,7 +342,7 @@ def _to_image(x, h, w, residual):
     b, n, c = x.shape
     if residual is not None and _is_channels_last(residual) and x.is_contiguous():
         # channels_last pipeline: the token tensor already is the NHWC image; the add stays a plain vectorised add
-        return x.view(b, h, w, c).permute(0, 3, 1, 2) + residual
+        return _native.residual_add(x.view(b, h, w, c).permute(0, 3, 1, 2), residual)
     if _fast_layout(x) and c % 8 == 0 and n % 8 == 0 and (residual is None or _fast_layout(residual)):
         return _native.transpose_add(x, residual).view(b, c, h, w)
     x = x.reshape(b, h, w, c).permute(0, 3, 1, 2).contiguous()
@@ -396,4 +396,4 @@ class SpatialTransformer(nn.Module):
         else:
             x = _to_image(x, h, w, None)
         x = self.proj_out(x)
-        return x + x_in
+        return _native.residual_add(x, x_in)

@@ -25,6 +25,8 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr",
     "-Xptxas", "-v",
 ]
+if os.environ.get("CGS_BUILD_TRACE") == "1":      # attention timeline stamps (tools/attn_trace.py); slower kernel
+    NVCC_FLAGS.append("-DCGS_ATTN_TRACING=1")
 
 
 def _nvcc() -> str:

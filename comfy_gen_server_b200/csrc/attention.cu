@@ -11,7 +11,9 @@
 // One CTA handles NQT query tiles of 128 rows for one (batch, head):
 //   warps [0, 4*NQT)          softmax warpgroups, one per query tile; thread == query row
 //   warp  4*NQT               TMA producer (Q once; K/V ring of KST stages, 128 keys per tile)
-//   warps 4*NQT+1 .. +NQT     one single-thread tcgen05.mma issuer per query tile (the first also owns TMEM).
+//   warps 4*NQT+1 .. +NQT     one single-thread tcgen05.mma issuer per query tile (the first also owns TMEM);
+//                             the service warpgroup is filled up to four warps and hands its registers to the
+//                             softmax warpgroups with setmaxnreg (40 vs 224 / 200 registers per thread).
 //                             One issuer for both tiles was the bottleneck of the first versions (~3100 cycles
 //                             of serial issue work per key tile, head-of-line blocking between the tiles).
 // Per key tile j and query tile t:
@@ -43,8 +45,28 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 128;
 constexpr int TILE_BYTES = 128 * 128;  // one [128 rows x 64 bf16] swizzled box
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
-constexpr int kPolyPairs = 1;    // of every kPolyPeriod element pairs, this many use the FMA-pipe exp2
-constexpr int kPolyPeriod = 4;
+#ifndef CGS_ATTN_SETMAXNREG
+#define CGS_ATTN_SETMAXNREG 1
+#endif
+// 4 * SPLIT softmax warps per query tile + one service warpgroup (TMA producer, one MMA issuer per tile, filler)
+template <int NQT, int SPLIT> constexpr int kThreads = (NQT * 4 * SPLIT + 4) * 32;
+constexpr int kRegsService = 40;
+// registers per softmax thread after the hand-over: what the launch gives every thread (64 K / threads per SM,
+// rounded down to 8) times all threads, minus the service warpgroup's share, over the softmax threads
+template <int NQT, int SPLIT> constexpr int kRegsLaunch = (65536 / (kThreads<NQT, SPLIT> * (NQT == 1 ? 2 : 1))) / 8 * 8;
+template <int NQT, int SPLIT> constexpr int kRegsSoftmax =
+    ((kRegsLaunch<NQT, SPLIT> * kThreads<NQT, SPLIT> - 128 * kRegsService) / (kThreads<NQT, SPLIT> - 128)) / 8 * 8;
+#ifndef CGS_ATTN_POLY_PAIRS          // tuning overrides for tools/attn_variants.py
+#define CGS_ATTN_POLY_PAIRS 1
+#endif
+#ifndef CGS_ATTN_POLY_PERIOD
+#define CGS_ATTN_POLY_PERIOD 4
+#endif
+#ifndef CGS_ATTN_SPLIT               // threads per score row: 1 (thread == row) or 2 (half a row each; measured
+#define CGS_ATTN_SPLIT 1             // 4-5 % slower at every shape, kept for tools/attn_variants.py)
+#endif
+constexpr int kPolyPairs = CGS_ATTN_POLY_PAIRS;    // of every kPolyPeriod element pairs, this many use the FMA-pipe exp2
+constexpr int kPolyPeriod = CGS_ATTN_POLY_PERIOD;
 }  // namespace attn
 
 struct AttnParams {
@@ -56,27 +78,45 @@ struct AttnParams {
     float scale_log2;
 };
 
+// The timeline stamps split the softmax loop into basic blocks and keep ptxas from overlapping its phases, so they
+// are compiled in only by `CGS_BUILD_TRACE=1 python comfy_gen_server_b200/build.py` (-DCGS_ATTN_TRACING=1).
+#ifndef CGS_ATTN_TRACING
+#define CGS_ATTN_TRACING 0
+#endif
+#if !CGS_ATTN_TRACING
+#define CGS_TRACE(role, j, e) do { } while (0)
+#define CGS_TRACE_CTA(e) do { } while (0)
+#else
 #define CGS_TRACE(role, j, e)                                                                      \
     do {                                                                                           \
         if (p.dbg != nullptr && trace_me && (j) < 64) p.dbg[((role) * 64 + (j)) * 8 + (e)] = clock64(); \
     } while (0)
 
-template <int NKB, int NQT, int KST>
+// whole-CTA events (entry, set-up done, epilogue begin/end, exit) of CTA (0,0,0), stamped by thread 0
+#define CGS_TRACE_CTA(e)                                                                            \
+    do {                                                                                            \
+        if (p.dbg != nullptr && (blockIdx.x | blockIdx.y | blockIdx.z | threadIdx.x) == 0)          \
+            p.dbg[(3 * 64 + 63) * 8 + (e)] = clock64();                                             \
+    } while (0)
+#endif
+
+template <int NKB, int NQT, int KST, int SPLIT>
 struct AttnSmem {
     static constexpr int Q_OFF = 0;
     static constexpr int K_OFF = Q_OFF + NQT * NKB * attn::TILE_BYTES;
     static constexpr int V_OFF = K_OFF + KST * NKB * attn::TILE_BYTES;
     static constexpr int BAR_OFF = V_OFF + KST * NKB * attn::TILE_BYTES;
     static constexpr int NBARS = 5 * NQT + 4 * KST;
-    static constexpr int BYTES = BAR_OFF + NBARS * 8 + 16 + 1024;
+    static constexpr int XCH_OFF = BAR_OFF + NBARS * 8 + 16;          // float [NQT][2 (parity)][SPLIT][128]
+    static constexpr int BYTES = XCH_OFF + (SPLIT > 1 ? NQT * 2 * SPLIT * 128 * 4 : 0) + 1024;
 };
 
-template <int NKB, int NQT, int KST>
-__global__ void __launch_bounds__((NQT * 5 + 1) * 32, (NQT == 1 ? 2 : 1))
+template <int NKB, int NQT, int KST, int SPLIT>
+__global__ void __launch_bounds__(attn::kThreads<NQT, SPLIT>, (NQT == 1 ? 2 : 1))
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
     using namespace attn;
-    using L = AttnSmem<NKB, NQT, KST>;
+    using L = AttnSmem<NKB, NQT, KST, SPLIT>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
@@ -92,10 +132,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint64_t* v_empty = v_full + KST;        // [KST]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(v_empty + KST);
 
+    CGS_TRACE_CTA(0);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    constexpr int PRODUCER_WARP = NQT * 4;
-    constexpr int MMA_WARP = NQT * 4 + 1;      // first of NQT issuer warps
+    constexpr int PRODUCER_WARP = NQT * 4 * SPLIT;
+    constexpr int MMA_WARP = PRODUCER_WARP + 1;      // first of NQT issuer warps
 
     const int q0 = blockIdx.x * (BLOCK_M * NQT);
     const int head = blockIdx.y;
@@ -119,9 +160,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             for (int t = 0; t < NQT; ++t) {
                 mbar_init(&q_full[t], 1);
                 mbar_init(&s_full[t], 1);
-                mbar_init(&p_full[t], 128);
+                mbar_init(&p_full[t], 128 * SPLIT);
                 mbar_init(&o_full[t], 1);
-                mbar_init(&s_free[t], 128);
+                mbar_init(&s_free[t], 128 * SPLIT);
             }
             for (int s = 0; s < KST; ++s) {
                 mbar_init(&k_full[s], 1);
@@ -139,7 +180,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    CGS_TRACE_CTA(1);
 
+    // Register hand-over between warpgroups (as in every warp-specialised Blackwell kernel): the TMA / MMA
+    // warpgroup needs a few dozen registers, the softmax threads hold a whole 128-column score row plus the packed
+    // probabilities. The launch gives every thread the same share (168 with 384 threads, 128 with 2 x 256).
+
+    if (warp >= PRODUCER_WARP) {
+#if CGS_ATTN_SETMAXNREG
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(attn::kRegsService));
+#endif
     if (warp == PRODUCER_WARP) {
         // ------------------------------------------------------------------ TMA producer
         if (elect_one()) {
@@ -166,7 +216,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
         }
         __syncwarp();
-    } else if (warp >= MMA_WARP) {
+    } else if (warp < MMA_WARP + NQT) {     // (the remaining warps only fill the service warpgroup up to four)
         // ------------------------------------------------------------------ MMA issuer for query tile t
         if (elect_one()) {
             const int t = warp - MMA_WARP;
@@ -252,19 +302,30 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
         }
         __syncwarp();
+    }
     } else {
-        // ------------------------------------------------------------------ softmax warpgroups
-        const int t = warp >> 2;
+        // ------------------------------------------------------------------ softmax warps
+        // SPLIT threads share a score row (COLS columns each). ncu on thread == row (two softmax warps per
+        // scheduler): issue active 51 %, XU 54 %, FMA 36 %, ALU 31 %, tensor 35 %; per warp and key tile ~745 issue
+        // cycles + ~800 cycles of fixed two-cycle stalls of the packed / half-rate instructions. Doubling the warps
+        // (SPLIT = 2) does not fill those slots: it measured 4-5 % slower.
+#if CGS_ATTN_SETMAXNREG
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(attn::kRegsSoftmax<NQT, SPLIT>));
+#endif
+        constexpr int COLS = BLOCK_N / SPLIT;
+        const int t = warp / (4 * SPLIT);
+        const int h = (warp >> 2) % SPLIT;          // which column part of the row
         const int quad = warp & 3;
         const int row_in_tile = quad * 32 + lane;
         const uint32_t lane_field = static_cast<uint32_t>(quad * 32) << 16;
-        const uint32_t s_addr = tmem_base + lane_field + S_COL + t * BLOCK_N;
-        const uint32_t p_addr = tmem_base + lane_field + P_COL + t * 64;
+        const uint32_t s_addr = tmem_base + lane_field + S_COL + t * BLOCK_N + h * COLS;
+        const uint32_t p_addr = tmem_base + lane_field + P_COL + t * 64 + h * (COLS / 2);
         const uint32_t o_addr = tmem_base + lane_field + O_COL + t * o_stride;
+        float* xch = reinterpret_cast<float*>(smem + L::XCH_OFF) + t * 2 * SPLIT * 128;
 
-        const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && quad == 0 && lane == 0;
+        const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && quad == 0 && lane == 0 && h == 0;
         float m_run = -INFINITY;  // running max, already multiplied by scale_log2
-        float l_run = 0.f;
+        float l_run = 0.f;        // this thread's part of the row sum
         const float scale = p.scale_log2;
         const uint64_t scale2 = pack_f32x2(scale, scale);
 
@@ -273,34 +334,40 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             mbar_wait(&s_full[t], j & 1);
             CGS_TRACE(t, j, 1);
             tc_fence_after();
-            uint32_t sr[128];
-            tmem_ld_x32(s_addr + 0, sr + 0);
-            tmem_ld_x32(s_addr + 32, sr + 32);
-            tmem_ld_x32(s_addr + 64, sr + 64);
-            tmem_ld_x32(s_addr + 96, sr + 96);
+            uint32_t sr[COLS];
+#pragma unroll
+            for (int c = 0; c < COLS; c += 32) tmem_ld_x32(s_addr + c, sr + c);
             tmem_wait_ld();
             // S(j) is in registers: give the buffer back so S(j+1) is computed during this softmax
             tc_fence_before();
             mbar_arrive(&s_free[t]);
             CGS_TRACE(t, j, 2);
 
-            const int n_valid = p.Nk - j * BLOCK_N;
-            if (n_valid < BLOCK_N) {
+            const int n_valid = p.Nk - j * BLOCK_N - h * COLS;
+            if (n_valid < COLS) {
 #pragma unroll
-                for (int i = 0; i < 128; ++i)
+                for (int i = 0; i < COLS; ++i)
                     if (i >= n_valid) sr[i] = 0xff800000u;  // -inf
             }
             float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-            for (int i = 0; i < 128; i += 8) {
+            for (int i = 0; i < COLS; i += 8) {
                 mx0 = fmax3(mx0, __uint_as_float(sr[i + 0]), __uint_as_float(sr[i + 1]));
                 mx1 = fmax3(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
                 mx2 = fmax3(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
                 mx3 = fmax3(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
             }
-            mx0 = fmax3(mx0, mx1, mx2);
-            mx1 = mx3;
-            const float m_new = fmaxf(mx0, mx1) * scale;
+            float mx = fmaxf(fmax3(mx0, mx1, mx2), mx3);
+            if constexpr (SPLIT > 1) {
+                // agree on the row max with the thread(s) holding the other columns (double-buffered by key-tile
+                // parity: the barrier of tile j+1 orders every read of tile j before the writes of tile j+2)
+                float* slot = xch + (j & 1) * SPLIT * 128;
+                slot[h * 128 + row_in_tile] = mx;
+                named_bar_sync(1 + t, 128 * SPLIT);
+#pragma unroll
+                for (int o = 1; o < SPLIT; ++o) mx = fmaxf(mx, slot[((h + o) % SPLIT) * 128 + row_in_tile]);
+            }
+            const float m_new = mx * scale;
 
             float alpha = 1.f;
             bool need_rescale = false;
@@ -313,43 +380,26 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 need_rescale = true;
             }
             const uint64_t negm2 = pack_f32x2(-m_run, -m_run);
-            uint32_t pr[64];
+            uint32_t pr[COLS / 2];
             uint64_t acc0 = 0ull, acc1 = 0ull;   // two packed (lo, hi) partial row sums
             CGS_TRACE(t, j, 3);
-            // phase 1: x = s * scale - m, in place, packed FFMA2
+            // x = s * scale - m (packed FFMA2); 2^x: the MUFU gives 16 lanes/clk/SM, so kPolyPairs of every
+            // kPolyPeriod pairs go to a degree-3 polynomial on the FMA pipe; row sum (packed FADD2); bf16 pack
 #pragma unroll
-            for (int i = 0; i < 64; ++i) {
+            for (int i = 0; i < COLS / 2; ++i) {
                 const uint64_t x2 = ffma2(pack_u32x2(sr[2 * i], sr[2 * i + 1]), scale2, negm2);
-                float lo, hi;
-                unpack_f32x2(x2, lo, hi);
-                sr[2 * i] = __float_as_uint(lo);
-                sr[2 * i + 1] = __float_as_uint(hi);
-            }
-            CGS_TRACE(t, j, 6);
-            // phase 2: 2^x. The MUFU (16 lanes/clk/SM, ~12 clk per warp instruction in situ) is the limiter of
-            // d = 64 attention, so kPolyPairs of every kPolyPeriod pairs are evaluated on the FMA pipe instead.
-            // All pairs are independent: the two pipes run side by side.
-#pragma unroll
-            for (int i = 0; i < 64; ++i) {
+                uint64_t e2;
                 if ((i % kPolyPeriod) < kPolyPairs) {
-                    uint32_t rlo, rhi;
-                    const uint64_t r = ex2_poly2(pack_u32x2(sr[2 * i], sr[2 * i + 1]));
-                    asm("mov.b64 {%0, %1}, %2;" : "=r"(rlo), "=r"(rhi) : "l"(r));
-                    sr[2 * i] = rlo;
-                    sr[2 * i + 1] = rhi;
+                    e2 = ex2_poly2(x2);
                 } else {
-                    sr[2 * i] = __float_as_uint(ex2_approx(__uint_as_float(sr[2 * i])));
-                    sr[2 * i + 1] = __float_as_uint(ex2_approx(__uint_as_float(sr[2 * i + 1])));
+                    float lo, hi;
+                    unpack_f32x2(x2, lo, hi);
+                    e2 = pack_f32x2(ex2_approx(lo), ex2_approx(hi));
                 }
-            }
-            CGS_TRACE(t, j, 7);
-            // phase 3: row sum (packed FADD2) and bf16 pack
-#pragma unroll
-            for (int i = 0; i < 64; i += 2) {
-                acc0 = fadd2(acc0, pack_u32x2(sr[2 * i], sr[2 * i + 1]));
-                acc1 = fadd2(acc1, pack_u32x2(sr[2 * i + 2], sr[2 * i + 3]));
-                pr[i] = pack_bf16x2(__uint_as_float(sr[2 * i]), __uint_as_float(sr[2 * i + 1]));
-                pr[i + 1] = pack_bf16x2(__uint_as_float(sr[2 * i + 2]), __uint_as_float(sr[2 * i + 3]));
+                if (i & 1) acc1 = fadd2(acc1, e2); else acc0 = fadd2(acc0, e2);
+                float elo, ehi;
+                unpack_f32x2(e2, elo, ehi);
+                pr[i] = pack_bf16x2(elo, ehi);
             }
             CGS_TRACE(t, j, 4);
             {
@@ -364,10 +414,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 mbar_wait(&o_full[t], (j - 1) & 1);
                 tc_fence_after();
             }
-            tmem_st_x32(p_addr + 0, pr + 0);
-            tmem_st_x32(p_addr + 32, pr + 32);
+#pragma unroll
+            for (int c = 0; c < COLS / 2; c += 32) tmem_st_x32(p_addr + c, pr + c);
             if (__any_sync(0xffffffffu, need_rescale)) {
-                for (int c = 0; c < (dv_n >> 4); ++c) {
+                for (int c = h; c < (dv_n >> 4); c += SPLIT) {      // the row's threads take alternate 16-column chunks
                     uint32_t orr[16];
                     tmem_ld_x16(o_addr + c * 16, orr);
                     tmem_wait_ld();
@@ -383,14 +433,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             CGS_TRACE(t, j, 5);
         }
 
-        // epilogue: O / l -> bf16 -> global
+        if constexpr (SPLIT > 1) {
+            // whole-row sum: one more exchange (parity slot of a tile that does not exist)
+            float* slot = xch + (n_tiles & 1) * SPLIT * 128;
+            slot[h * 128 + row_in_tile] = l_run;
+            named_bar_sync(1 + t, 128 * SPLIT);
+#pragma unroll
+            for (int o = 1; o < SPLIT; ++o) l_run += slot[((h + o) % SPLIT) * 128 + row_in_tile];
+        }
+
+        // epilogue: O / l -> bf16 -> global (the row's threads take alternate 16-column chunks)
         mbar_wait(&o_full[t], (n_tiles - 1) & 1);
         tc_fence_after();
+        CGS_TRACE_CTA(2);
         const float inv_l = 1.f / l_run;
         const int q_row = q0 + t * BLOCK_M + row_in_tile;
         __nv_bfloat16* orow = p.out + (long long)batch * p.o_stride_b +
                               (long long)q_row * p.o_stride_n + (long long)head * p.o_stride_h;
-        for (int c = 0; c < (dv_n >> 4); ++c) {
+        for (int c = h; c < (dv_n >> 4); c += SPLIT) {
             uint32_t orr[16];
             tmem_ld_x16(o_addr + c * 16, orr);
             tmem_wait_ld();
@@ -410,20 +470,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
         }
         tc_fence_before();
+        CGS_TRACE_CTA(3);
     }
 
     __syncthreads();
+    CGS_TRACE_CTA(4);
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
-template <int NKB, int NQT, int KST>
+template <int NKB, int NQT, int KST, int SPLIT = CGS_ATTN_SPLIT>
 static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                        const AttnParams& p, cudaStream_t stream) {
-    using L = AttnSmem<NKB, NQT, KST>;
-    auto kern = attn_fwd_kernel<NKB, NQT, KST>;
+    using L = AttnSmem<NKB, NQT, KST, SPLIT>;
+    auto kern = attn_fwd_kernel<NKB, NQT, KST, SPLIT>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
     dim3 grid((p.Nq + attn::BLOCK_M * NQT - 1) / (attn::BLOCK_M * NQT), p.H, p.B);
-    kern<<<grid, (NQT * 5 + 1) * 32, L::BYTES, stream>>>(tq, tk, tv, p);
+    kern<<<grid, attn::kThreads<NQT, SPLIT>, L::BYTES, stream>>>(tq, tk, tv, p);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }
@@ -487,7 +549,8 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     const int n_tiles = (Nk + attn::BLOCK_N - 1) / attn::BLOCK_N;
     // Two query tiles per CTA (ping-pong) for long key sequences; one tile per CTA with a single K/V
     // stage for short ones (text cross-attention, tiny levels): small SMEM/TMEM footprint, 2 CTAs per SM.
-    bool two_tiles = Nq > attn::BLOCK_M && n_tiles > 2 && 2 * (192 + dv_n) <= 512;
+    // (up to 8 key tiles the set-up and epilogue of a CTA are a quarter of its life; two small CTAs per SM hide them)
+    bool two_tiles = Nq > attn::BLOCK_M && n_tiles > 8 && 2 * (192 + dv_n) <= 512;
     if (const char* e = getenv("CGS_ATTN_MAX_TILES_1CTA")) {     // experiment knob: one query tile per CTA up to this many key tiles
         if (n_tiles <= atoi(e)) two_tiles = false;
     }

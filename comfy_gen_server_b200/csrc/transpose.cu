@@ -60,7 +60,48 @@ transpose_add_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* 
     }
 }
 
+// out = a + b for two bf16 tensors with identical dense layouts (the ResBlock's `skip_connection(x) + h`,
+// openaimodel.py:264, and the SpatialTransformer's `x + x_in` in the channels-last pipeline). ATen sends these adds
+// down its strided, non-vectorised path when the operands are channels_last views (2.7 TB/s measured); this is the
+// plain 16-byte-per-thread streaming form.
+__global__ void __launch_bounds__(256)
+add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out, long long n8) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n8) return;
+    uint4 x = a[i];
+    const uint4 y = b[i];
+    __nv_bfloat162* xv = reinterpret_cast<__nv_bfloat162*>(&x);
+    const __nv_bfloat162* yv = reinterpret_cast<const __nv_bfloat162*>(&y);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) xv[k] = __hadd2_rn(xv[k], yv[k]);
+    out[i] = x;
+}
+
 }  // namespace cgs
+
+extern "C" int cgs_add_fwd(const void* a, const void* b, void* out, long long n, void* stream) {
+    using namespace cgs;
+    if (n < 0) {
+        set_last_error("add: negative size");
+        return kBadArgument;
+    }
+    if (n == 0) return kOk;
+    if (n % 8 != 0 || ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
+                        reinterpret_cast<uintptr_t>(out)) & 0xF)) {
+        set_last_error("add: element count must be a multiple of 8 and pointers 16-byte aligned");
+        return kUnsupportedShape;
+    }
+    const long long n8 = n / 8;
+    const long long blocks = (n8 + 255) / 256;
+    if (blocks > 0x7fffffffLL) {
+        set_last_error("add: tensor too large");
+        return kUnsupportedShape;
+    }
+    add_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), n8);
+    CGS_CUDA_CHECK(cudaGetLastError());
+    return kOk;
+}
 
 extern "C" int cgs_transpose_add_fwd(const void* in, const void* residual, void* out, int N, int R, int C,
                                      void* stream) {

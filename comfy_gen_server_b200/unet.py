@@ -14,6 +14,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from . import _native
 from .attention import SpatialTransformer
 from .ops import b200_ops
 
@@ -111,7 +112,7 @@ class ResBlock(TimestepBlock):
         h = self.in_layers[2](_norm_silu(self.in_layers[0], x))
         emb_out = self.emb_layers(emb).type(h.dtype)
         h = self.out_layers[3](self.out_layers[2](_norm_silu(self.out_layers[0], h, emb_out.contiguous())))
-        return self.skip_connection(x) + h
+        return _native.residual_add(self.skip_connection(x), h)
 
 
 def forward_timestep_embed(ts, x, emb, context=None, transformer_options={}, output_shape=None):

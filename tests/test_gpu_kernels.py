@@ -204,6 +204,19 @@ def test_transpose_add_exact(N_, R, C):
     assert torch.equal(N().transpose_add(x, r), x.transpose(1, 2).contiguous() + r)
 
 
+def test_residual_add_layouts():
+    n = N()
+    a, b = bf(randn((2, 320, 16, 16), 1)), bf(randn((2, 320, 16, 16), 2))
+    assert torch.equal(n.residual_add(a, b), a + b)
+    acl, bcl = a.contiguous(memory_format=torch.channels_last), b.contiguous(memory_format=torch.channels_last)
+    out = n.residual_add(acl, bcl)
+    assert out.is_contiguous(memory_format=torch.channels_last) and torch.equal(out, a + b)
+    assert torch.equal(n.residual_add(acl, b), a + b)            # mixed layouts: falls back to torch's add
+    tok = bf(randn((2, 256, 320), 3))
+    img = tok.view(2, 16, 16, 320).permute(0, 3, 1, 2)            # the channels-last view used by SpatialTransformer
+    assert torch.equal(n.residual_add(img, acl), img + acl)
+
+
 def test_groupnorm_errors():
     n = N()
     w = bf(torch.ones(64))
