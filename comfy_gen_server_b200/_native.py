@@ -28,7 +28,7 @@ _SIGNATURES = {
     "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_fwd": [_c_void_p] * 6 + [_c_ll] + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_noalloc_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
-    "cgs_add_fwd": [_c_void_p] * 3 + [_c_ll, _c_void_p],
+    "cgs_add_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_ll, _c_void_p],
     "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
@@ -273,17 +273,30 @@ def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
             and (a.is_contiguous() or (a.dim() == 4 and a.is_contiguous(memory_format=torch.channels_last))))
 
 
-def residual_add(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
-    """a + b for bf16 CUDA tensors with one shared dense layout (contiguous or channels_last); anything else is a
-    plain torch add (the reference's own path for this op)."""
+def residual_add(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """a + b (+ bias[None, :, None, None]) for bf16 CUDA tensors with one shared dense layout (contiguous or
+    channels_last); anything else is a plain torch add (the reference's own path for this op)."""
     if (a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and b.is_cuda
             and _same_dense_layout(a, b) and a.numel() % 8 == 0):
+        channels, inner, bias_ptr = 0, 1, None
+        if bias is not None:
+            channels = a.shape[1]
+            nhwc = not a.is_contiguous()
+            inner = 1 if nhwc else a.numel() // (a.shape[0] * channels)
+            if (bias.dtype != torch.bfloat16 or bias.numel() != channels or (channels % 8 if nhwc else inner % 8)):
+                return a + b + bias.to(a.dtype).view(1, -1, *([1] * (a.dim() - 2)))
+            bias = bias.contiguous()
+            bias_ptr = bias.data_ptr()
         out = torch.empty_like(a)
         with _Launch("residual_add", a, 6.0 * a.numel()):
-            rc = load_library().cgs_add_fwd(a.data_ptr(), b.data_ptr(), out.data_ptr(), a.numel(), _stream(a))
+            rc = load_library().cgs_add_fwd(a.data_ptr(), b.data_ptr(), bias_ptr, out.data_ptr(), a.numel(),
+                                            channels, inner, _stream(a))
         _check(rc, "cgs_add_fwd")
         return out
-    return a + b
+    out = a + b
+    if bias is not None:
+        out = out + bias.to(out.dtype).view(1, -1, *([1] * (out.dim() - 2)))
+    return out
 
 
 def transpose_add(x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:

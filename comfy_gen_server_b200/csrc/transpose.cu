@@ -60,26 +60,57 @@ transpose_add_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* 
     }
 }
 
-// out = a + b for two bf16 tensors with identical dense layouts (the ResBlock's `skip_connection(x) + h`,
-// openaimodel.py:264, and the SpatialTransformer's `x + x_in` in the channels-last pipeline). ATen sends these adds
-// down its strided, non-vectorised path when the operands are channels_last views (2.7 TB/s measured); this is the
-// plain 16-byte-per-thread streaming form.
+// out = a + b (+ bias[channel]) for two bf16 tensors with identical dense layouts (the ResBlock's
+// `skip_connection(x) + h`, openaimodel.py:264, and the SpatialTransformer's `x + x_in` in the channels-last
+// pipeline). ATen sends these adds down its strided, non-vectorised path when the operands are channels_last views
+// (2.7 TB/s measured); this is the plain 16-byte-per-thread streaming form. The optional per-channel bias is the
+// bias of the convolution that produced b (and of a 1x1 skip convolution): cuDNN's fprop has no bias epilogue
+// through ATen, which adds it in a separate full pass; here it rides along. channel = (i / inner) % channels with
+// inner = 1 for channels_last (8 consecutive channels per thread) and H*W for NCHW (one channel per thread).
+template <bool BIAS>
 __global__ void __launch_bounds__(256)
-add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out, long long n8) {
+add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const __nv_bfloat16* __restrict__ bias,
+           uint4* __restrict__ out, long long n8, int channels, int inner) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n8) return;
-    uint4 x = a[i];
+    const uint4 x = a[i];
     const uint4 y = b[i];
-    __nv_bfloat162* xv = reinterpret_cast<__nv_bfloat162*>(&x);
+    const __nv_bfloat162* xv = reinterpret_cast<const __nv_bfloat162*>(&x);
     const __nv_bfloat162* yv = reinterpret_cast<const __nv_bfloat162*>(&y);
+    uint4 r;
+    __nv_bfloat162* rv = reinterpret_cast<__nv_bfloat162*>(&r);
+    if constexpr (BIAS) {
+        float bf[8];
+        if (inner == 1) {
+            const uint4 bb = *reinterpret_cast<const uint4*>(bias + (i * 8) % channels);
+            const __nv_bfloat162* bv = reinterpret_cast<const __nv_bfloat162*>(&bb);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) xv[k] = __hadd2_rn(xv[k], yv[k]);
-    out[i] = x;
+            for (int k = 0; k < 4; ++k) {
+                const float2 f = __bfloat1622float2(bv[k]);
+                bf[2 * k] = f.x;
+                bf[2 * k + 1] = f.y;
+            }
+        } else {
+            const float v = __bfloat162float(bias[((i * 8) / inner) % channels]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) bf[k] = v;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 fx = __bfloat1622float2(xv[k]), fy = __bfloat1622float2(yv[k]);
+            rv[k] = __floats2bfloat162_rn(fx.x + fy.x + bf[2 * k], fx.y + fy.y + bf[2 * k + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) rv[k] = __hadd2_rn(xv[k], yv[k]);
+    }
+    out[i] = r;
 }
 
 }  // namespace cgs
 
-extern "C" int cgs_add_fwd(const void* a, const void* b, void* out, long long n, void* stream) {
+extern "C" int cgs_add_fwd(const void* a, const void* b, const void* bias, void* out, long long n, int channels,
+                           long long inner, void* stream) {
     using namespace cgs;
     if (n < 0) {
         set_last_error("add: negative size");
@@ -91,14 +122,30 @@ extern "C" int cgs_add_fwd(const void* a, const void* b, void* out, long long n,
         set_last_error("add: element count must be a multiple of 8 and pointers 16-byte aligned");
         return kUnsupportedShape;
     }
+    if (bias != nullptr) {
+        const bool nhwc_ok = inner == 1 && channels > 0 && channels % 8 == 0 &&
+                             (reinterpret_cast<uintptr_t>(bias) & 0xF) == 0;
+        const bool nchw_ok = inner > 1 && inner % 8 == 0 && inner <= 0x7fffffffLL && channels > 0;
+        if (!nhwc_ok && !nchw_ok) {
+            set_last_error("add: bias needs channels %% 8 == 0 (channels_last, inner 1) or H*W %% 8 == 0 (NCHW); "
+                           "got channels=%d inner=%lld", channels, inner);
+            return kUnsupportedShape;
+        }
+    }
     const long long n8 = n / 8;
     const long long blocks = (n8 + 255) / 256;
     if (blocks > 0x7fffffffLL) {
         set_last_error("add: tensor too large");
         return kUnsupportedShape;
     }
-    add_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), n8);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (bias != nullptr)
+        add_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(
+            static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<const __nv_bfloat16*>(bias),
+            static_cast<uint4*>(out), n8, channels, (int)inner);
+    else
+        add_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(
+            static_cast<const uint4*>(a), static_cast<const uint4*>(b), nullptr, static_cast<uint4*>(out), n8, 0, 1);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }

@@ -100,6 +100,12 @@ class b200_ops:
                 return self.forward_comfy_cast_weights(*args, **kwargs)
             return super().forward(*args, **kwargs)
 
+        def forward_nobias(self, input):
+            """The convolution without its bias: ATen adds a cuDNN convolution's bias in a separate full pass, so
+            the ResBlock hands the bias to the kernel that consumes this output instead (GroupNorm's add_nc, the
+            residual add)."""
+            return self._conv_forward(input, self.weight, None)
+
     class Conv3d(torch.nn.Conv3d, CastWeightBiasOp):
         def reset_parameters(self):
             return None

@@ -108,7 +108,24 @@ class ResBlock(TimestepBlock):
         else:
             self.skip_connection = operations.conv_nd(dims, channels, self.out_channels, 1, dtype=dtype, device=device)
 
+    def _fold_bias(self, x):
+        """Conv biases ride along in the consumers of the conv outputs when everything is resident bf16 on CUDA."""
+        convs = [self.in_layers[2], self.out_layers[3]]
+        if not isinstance(self.skip_connection, nn.Identity):
+            convs.append(self.skip_connection)
+        return (x.is_cuda and x.dtype == torch.bfloat16 and hasattr(self.out_layers[0], "forward_fused")
+                and all(hasattr(c, "forward_nobias") and not c.comfy_cast_weights and c.bias is not None
+                        and c.bias.dtype == torch.bfloat16 for c in convs))
+
     def forward(self, x, emb):
+        if self._fold_bias(x):
+            conv1, conv2, skip = self.in_layers[2], self.out_layers[3], self.skip_connection
+            h = conv1.forward_nobias(_norm_silu(self.in_layers[0], x))
+            emb_out = self.emb_layers(emb).type(h.dtype) + conv1.bias          # [N, C]: conv1's bias joins the embedding
+            h = conv2.forward_nobias(self.out_layers[2](_norm_silu(self.out_layers[0], h, emb_out.contiguous())))
+            if isinstance(skip, nn.Identity):
+                return _native.residual_add(x, h, conv2.bias)
+            return _native.residual_add(skip.forward_nobias(x), h, conv2.bias + skip.bias)
         h = self.in_layers[2](_norm_silu(self.in_layers[0], x))
         emb_out = self.emb_layers(emb).type(h.dtype)
         h = self.out_layers[3](self.out_layers[2](_norm_silu(self.out_layers[0], h, emb_out.contiguous())))

@@ -124,11 +124,15 @@ int cgs_groupnorm_nhwc_noalloc_fwd(const void* x, const void* add_nc, const void
 int cgs_transpose_add_fwd(const void* in, const void* residual, void* out, int N, int R, int C, void* stream);
 
 /*
- * out = a + b, bf16, n elements (n % 8 == 0, 16-byte aligned), for two tensors that share one dense memory layout.
- * Replaces the ResBlock's `self.skip_connection(x) + h` (comfy/ldm/modules/diffusionmodules/openaimodel.py:264) and
- * the SpatialTransformer's `x + x_in` (comfy/ldm/modules/attention.py:639). out may alias a or b.
+ * out = a + b (+ bias[channel]), bf16, n elements (n % 8 == 0, 16-byte aligned), for two tensors that share one dense
+ * memory layout. Replaces the ResBlock's `self.skip_connection(x) + h` (comfy/ldm/modules/diffusionmodules/
+ * openaimodel.py:264) and the SpatialTransformer's `x + x_in` (comfy/ldm/modules/attention.py:639). bias (may be NULL)
+ * is the [channels] bias of the convolution(s) that produced the operands -- torch.nn.Conv2d's separate bias pass
+ * (openaimodel.py:181, 217, 228 via ops.Conv2d) folded into this one; channel of element i = (i / inner) % channels,
+ * inner = 1 for channels_last (channels % 8 == 0), H*W for NCHW (H*W % 8 == 0). out may alias a or b.
  */
-int cgs_add_fwd(const void* a, const void* b, void* out, long long n, void* stream);
+int cgs_add_fwd(const void* a, const void* b, const void* bias, void* out, long long n, int channels, long long inner,
+                void* stream);
 
 /*
  * GEGLU projection (G1): y[m, n] = (x W^T + b)[m, n] * gelu_erf((x W^T + b)[m, N + n]).

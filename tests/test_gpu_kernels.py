@@ -215,6 +215,36 @@ def test_residual_add_layouts():
     tok = bf(randn((2, 256, 320), 3))
     img = tok.view(2, 16, 16, 320).permute(0, 3, 1, 2)            # the channels-last view used by SpatialTransformer
     assert torch.equal(n.residual_add(img, acl), img + acl)
+    # per-channel bias (the folded conv bias): one rounding of the fp32 sum
+    bias = bf(randn((320,), 4))
+    want = (a.float() + b.float() + bias.float().view(1, -1, 1, 1)).to(torch.bfloat16)
+    assert torch.equal(n.residual_add(a, b, bias), want)
+    out = n.residual_add(acl, bcl, bias)
+    assert out.is_contiguous(memory_format=torch.channels_last) and torch.equal(out, want)
+    a2, b2 = bf(randn((2, 12, 3, 4), 5)), bf(randn((2, 12, 3, 4), 6))     # H*W and C not multiples of 8: torch path
+    want2 = a2 + b2 + bf(randn((12,), 7)).view(1, -1, 1, 1)
+    assert torch.equal(n.residual_add(a2, b2, bf(randn((12,), 7))), want2)
+
+
+def test_resblock_bias_folding_matches_plain_path():
+    """ResBlock with conv biases folded into GroupNorm's add_nc / the residual add vs the same block run op by op."""
+    from comfy_gen_server_b200 import unet
+    from comfy_gen_server_b200.ops import b200_ops
+    torch.manual_seed(0)
+    for cin, cout, cl in ((320, 320, False), (320, 640, True), (640, 320, True)):
+        blk = unet.ResBlock(cin, 1280, 0.0, out_channels=cout, dtype=torch.bfloat16, device="cuda", operations=b200_ops)
+        for prm in blk.parameters():
+            torch.nn.init.normal_(prm, std=0.05)
+        x = bf(randn((2, cin, 16, 16), 11))
+        emb = bf(randn((2, 1280), 12))
+        if cl:
+            blk = blk.to(memory_format=torch.channels_last)
+            x = x.contiguous(memory_format=torch.channels_last)
+        got = blk(x, emb)
+        blk._fold_bias = lambda _x: False
+        want = blk(x, emb)
+        err = (got.float() - want.float()).abs().max().item()
+        assert err <= 4 * ulp_tol(want), (cin, cout, cl, err)
 
 
 def test_groupnorm_errors():
