@@ -37,6 +37,8 @@ _SIGNATURES = {
                                               _c_ll, _c_ll, _c_void_p],
     "cgs_sampler_step_euler": [_c_void_p, _c_void_p, _c_float, _c_float, _c_void_p, _c_ll, _c_void_p],
     "cgs_sampler_step_dpmpp2m": [_c_void_p] * 3 + [_c_float] * 4 + [_c_void_p, _c_ll, _c_void_p],
+    "cgs_cfg_sampler_tail_dev_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
+                                                       _c_void_p, _c_void_p, _c_void_p, _c_ll, _c_ll, _c_void_p],
     "cgs_cfg_sampler_tail_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                                    _c_int] + [_c_float] * 4 + [_c_void_p, _c_void_p,
                                                                                _c_ll, _c_ll, _c_void_p],
@@ -481,6 +483,33 @@ def cfg_sampler_tail(x, model_out_uncond, model_out_cond, sigma, cond_scale: flo
             denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
     _check(rc, "cgs_cfg_sampler_tail_fwd")
     return denoised, x_next
+
+
+def cfg_sampler_tail_dev(x, model_out_uncond, model_out_cond, sigma, cond_scale: float, pred_type: int,
+                         old_denoised, step: torch.Tensor, denoised: torch.Tensor, x_next: torch.Tensor,
+                         sigma_data: float = 1.0):
+    """cfg_sampler_tail with the sampler mode / coefficients in device memory (`step`: fp32 [5] = mode, c0..c3) and
+    caller-owned outputs: the launch is the same for every step, so it can sit in a replayed CUDA graph."""
+    for name, t in (("tail x", x), ("tail sigma", sigma), ("tail old_denoised", old_denoised), ("tail step", step),
+                    ("tail denoised", denoised), ("tail x_next", x_next)):
+        _flat_f32(name, t)
+    if step.numel() < 5:
+        raise ValueError("tail step: need 5 floats (mode, c0..c3)")
+    u_ptr, c_ptr, is_bf16 = _model_out_ptrs(model_out_uncond, model_out_cond)
+    B = x.shape[0]
+    per = x.numel() // B if B else 0
+    with _Launch("cfg_sampler_tail", x, float(x.numel()) * (16 + 4 * (2 if is_bf16 else 4) // 2)):
+        rc = load_library().cgs_cfg_sampler_tail_dev_fwd(
+            x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(), cond_scale, pred_type, sigma_data,
+            old_denoised.data_ptr(), step.data_ptr(), denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
+    _check(rc, "cgs_cfg_sampler_tail_dev_fwd")
+    return denoised, x_next
+
+
+def add_replayed_launches(counts: dict) -> None:
+    """A replayed CUDA graph launches our kernels without passing through the wrappers: account for them."""
+    for family, n in counts.items():
+        LAUNCHES[family] = LAUNCHES.get(family, 0) + n
 
 
 # ----------------------------------------------------------------------------------------------

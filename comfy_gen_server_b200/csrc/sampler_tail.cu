@@ -83,7 +83,16 @@ tail_kernel(const float* __restrict__ x, const void* __restrict__ out_uncond,
             const void* __restrict__ out_cond, const float* __restrict__ sigma,
             const float* __restrict__ d_old, float* __restrict__ denoised,
             float* __restrict__ x_next, long long n4, long long per_sample4, float cond_scale,
-            float sigma_data, int pred_type, int mode, TailCoef k) {
+            float sigma_data, int pred_type, int mode, TailCoef k, const float* __restrict__ dev_step) {
+    if (dev_step != nullptr) {
+        // sampler mode and coefficients of this step live in device memory: the launch (and a CUDA graph holding it)
+        // is the same for every step of the schedule
+        mode = static_cast<int>(__ldg(dev_step));
+        k.c0 = __ldg(dev_step + 1);
+        k.c1 = __ldg(dev_step + 2);
+        k.c2 = __ldg(dev_step + 3);
+        k.c3 = __ldg(dev_step + 4);
+    }
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
          i += (long long)gridDim.x * blockDim.x) {
         const float4 xv = __ldg(reinterpret_cast<const float4*>(x) + i);
@@ -169,7 +178,8 @@ static int check_tail_shape(const char* who, long long batch, long long per_samp
 static int launch_tail(const float* x, const void* ou, const void* oc, int out_is_bf16,
                        const float* sigma, const float* d_old, float* denoised, float* x_next,
                        long long batch, long long per_sample, float cond_scale, float sigma_data,
-                       int pred_type, int mode, TailCoef k, cudaStream_t stream) {
+                       int pred_type, int mode, TailCoef k, cudaStream_t stream,
+                       const float* dev_step = nullptr) {
     int rc = check_tail_shape("sampler tail", batch, per_sample);
     if (rc != kOk) return rc;
     const long long n4 = batch * per_sample / 4;
@@ -182,11 +192,11 @@ static int launch_tail(const float* x, const void* ou, const void* oc, int out_i
     if (out_is_bf16)
         tail_kernel<true><<<grid, 256, 0, stream>>>(x, ou, oc, sigma, d_old, denoised, x_next, n4,
                                                     per_sample / 4, cond_scale, sigma_data,
-                                                    pred_type, mode, k);
+                                                    pred_type, mode, k, dev_step);
     else
         tail_kernel<false><<<grid, 256, 0, stream>>>(x, ou, oc, sigma, d_old, denoised, x_next, n4,
                                                      per_sample / 4, cond_scale, sigma_data,
-                                                     pred_type, mode, k);
+                                                     pred_type, mode, k, dev_step);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }
@@ -259,4 +269,21 @@ extern "C" int cgs_cfg_sampler_tail_fwd(const float* x, const void* out_uncond,
     return cgs::launch_tail(x, out_uncond, out_cond, out_is_bf16, sigma, old_denoised, denoised,
                             x_next, batch, per_sample, cond_scale, sigma_data, pred_type, sampler,
                             TailCoef{c0, c1, c2, c3}, static_cast<cudaStream_t>(stream));
+}
+
+// The same tail with the step's sampler mode and coefficients read from device memory: step[0] = mode (1, 2 or 3 as
+// a float), step[1..4] = c0..c3. old_denoised must always be a valid buffer (it is read only in mode 3).
+extern "C" int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_uncond,
+                                            const void* out_cond, int out_is_bf16, const float* sigma,
+                                            float cond_scale, int pred_type, float sigma_data,
+                                            const float* old_denoised, const float* step,
+                                            float* denoised, float* x_next, long long batch,
+                                            long long per_sample, void* stream) {
+    if (out_cond == nullptr || old_denoised == nullptr || step == nullptr) {
+        cgs::set_last_error("cfg_sampler_tail_dev: out_cond, old_denoised and step must not be null");
+        return cgs::kBadArgument;
+    }
+    return cgs::launch_tail(x, out_uncond, out_cond, out_is_bf16, sigma, old_denoised, denoised,
+                            x_next, batch, per_sample, cond_scale, sigma_data, pred_type, cgs::kTailDpmpp2m,
+                            TailCoef{0, 0, 0, 0}, static_cast<cudaStream_t>(stream), step);
 }

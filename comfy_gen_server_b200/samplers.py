@@ -15,6 +15,8 @@ ControlNet / GLIGEN side networks are outside this hot path (SURVEY.md section 2
 from __future__ import annotations
 
 import collections
+import logging
+import time
 import math
 
 import torch
@@ -471,13 +473,15 @@ class CFGGuider:
             "copies": len(parts), "context": cat["c_crossattn"].to(dt).contiguous(),
             "y": cat["y"].to(dt).contiguous() if "y" in cat else None,
             "cond_or_uncond": order, "batch": b, "tables": None,
+            # CUDA-graph replay of the whole step ("auto": only when the host, not the GPU, limits the step)
+            "calls": 0, "graph": None, "graph_opt": model_options.get("cuda_graph", "auto"), "probe": None,
         }
         if sig is not None:
             valid = sig[sig > 0]
             ts = torch.zeros(len(sig))
             ts[:len(valid)] = ms.timestep(valid).float()
             state["tables"] = (sig.view(-1, 1).repeat(1, b).to(dev),
-                               ts.view(-1, 1).repeat(1, b * len(parts)).to(dev), sig.clone())
+                               ts.view(-1, 1).repeat(1, b * len(parts)).to(dev), sig.clone(), ts)
         return state
 
     def _select_parts(self, parts, use_uncond):
@@ -501,6 +505,16 @@ class CFGGuider:
         ms = m.model_sampling
         tables = st["tables"]
         sigma_f = float(sigma_hat)
+        st["calls"] += 1
+        if st["graph"] is None and st["calls"] >= 2:
+            st["graph"] = self._maybe_capture_step(st, x, model_options)
+        if st["graph"]:
+            return self._graph_step(st, x, i, sigma_f, sampler, c0, c1, c2, c3, old_denoised)
+        probe = st["calls"] == 1 and st["graph_opt"] == "auto"
+        if probe:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
+            t_host = time.perf_counter()
         if tables is not None and i < len(tables[2]) and float(tables[2][i]) == sigma_f:
             sigma_vec, t_vec = tables[0][i], tables[1][i]
         else:
@@ -515,8 +529,97 @@ class CFGGuider:
         if not out.is_contiguous():          # channels_last UNets: the 4-channel output is tiny, make it NCHW
             out = out.contiguous()
         out_u, out_c = self._split_outputs(out, x.shape[0], st)
-        return _native.cfg_sampler_tail(x, out_u, out_c, sigma_vec, float(self.cfg), ms.pred_type, old_denoised,
-                                        sampler, c0, c1, c2, c3, float(ms.sigma_data))
+        res = _native.cfg_sampler_tail(x, out_u, out_c, sigma_vec, float(self.cfg), ms.pred_type, old_denoised,
+                                       sampler, c0, c1, c2, c3, float(ms.sigma_data))
+        if probe:
+            st["probe"] = ((time.perf_counter() - t_host) * 1e3, ev)
+            ev[1].record()
+        return res
+
+    # -- CUDA-graph replay of the step -------------------------------------------------------------
+    # One denoise step is ~1100 kernel launches (SDXL); the host needs ~24 ms to enqueue them. With eight 1024^2
+    # images per GPU the GPU works 120 ms on them and the host never matters; with one image the GPU is done in
+    # 15 ms and waits for the host. The step is shape-static and, once the sampler coefficients are read from device
+    # memory (cgs_cfg_sampler_tail_dev_fwd), identical for every step of the schedule: capture it once, replay it.
+    def _maybe_capture_step(self, st, x, model_options):
+        opt = st["graph_opt"]
+        if opt is False or opt is None or type(self) is not CFGGuider or _native._timed_family is not None:
+            return False
+        if opt == "auto":
+            if st["probe"] is None:
+                return False
+            host_ms, ev = st["probe"]
+            ev[1].synchronize()
+            if host_ms < 0.8 * ev[0].elapsed_time(ev[1]):      # the GPU is the limiter: nothing to gain
+                return False
+        try:
+            return self._capture_step(st, x, model_options)
+        except Exception as e:      # capture is an optimisation of the same native path; run it launch by launch
+            logging.warning("CUDA graph capture of the denoise step failed (%s); continuing without it", e)
+            return False
+
+    def _capture_step(self, st, x, model_options):
+        m = self.inner_model
+        ms = m.model_sampling
+        b, copies = x.shape[0], st["copies"]
+        n_par = b + b * copies + 8                    # [sigma x b | timestep x b*copies | mode, c0..c3, pad]
+        g = {
+            "P": torch.zeros(n_par, device=x.device, dtype=torch.float32),
+            "X": torch.empty_like(x), "XN": torch.empty_like(x), "DEN": torch.empty_like(x),
+            "OLD": torch.zeros_like(x), "stage": torch.zeros(64, n_par, dtype=torch.float32).pin_memory(),
+            "last_den": None,
+        }
+        sigma_vec, t_vec, step = g["P"][:b], g["P"][b:b + b * copies], g["P"][b + b * copies:]
+        topt = dict(model_options.get("transformer_options", {}))
+        topt["cond_or_uncond"] = list(st["cond_or_uncond"])
+        topt["sigmas"] = sigma_vec
+        cfg, sigma_data = float(self.cfg), float(ms.sigma_data)
+
+        def body():
+            xc = _native.unet_input(g["X"], sigma_vec, copies, sigma_data)
+            out = m.unet_raw(xc, t_vec, st["context"], st["y"], topt)
+            if not out.is_contiguous():
+                out = out.contiguous()
+            out_u, out_c = self._split_outputs(out, b, st)
+            _native.cfg_sampler_tail_dev(g["X"], out_u, out_c, sigma_vec, cfg, ms.pred_type, g["OLD"], step,
+                                         g["DEN"], g["XN"], sigma_data)
+            g["OLD"].copy_(g["DEN"])                     # the next step's old_denoised
+
+        before = dict(_native.LAUNCHES)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            body()
+        # capture launched nothing; remember what one replay launches
+        g["counts"] = {k: v - before.get(k, 0) for k, v in _native.LAUNCHES.items() if v != before.get(k, 0)}
+        for k, v in g["counts"].items():
+            _native.LAUNCHES[k] -= v
+        g["graph"] = graph
+        return g
+
+    def _graph_step(self, st, x, i, sigma_f, sampler, c0, c1, c2, c3, old_denoised):
+        g = st["graph"]
+        b, copies = x.shape[0], st["copies"]
+        if i >= g["stage"].shape[0]:
+            grown = torch.zeros(2 * (i + 1), g["stage"].shape[1], dtype=torch.float32).pin_memory()
+            grown[:g["stage"].shape[0]] = g["stage"]
+            g["stage"] = grown
+        tables = st["tables"]
+        if tables is not None and i < len(tables[2]) and float(tables[2][i]) == sigma_f:
+            t = float(tables[3][i])
+        else:
+            t = float(self.inner_model.model_sampling.timestep(torch.tensor([sigma_f]))[0])
+        row = g["stage"][i]                              # one pinned row per step: never rewritten while in flight
+        row[:b] = sigma_f
+        row[b:b + b * copies] = t
+        row[b + b * copies:b + b * copies + 5] = torch.tensor([float(sampler), c0, c1, c2, c3])
+        g["P"].copy_(row, non_blocking=True)
+        g["X"].copy_(x)
+        if sampler == 3 and old_denoised is not None and old_denoised is not g["last_den"]:
+            g["OLD"].copy_(old_denoised)                 # first replayed step: denoised of the last eager step
+        g["graph"].replay()
+        _native.add_replayed_launches(g["counts"])
+        g["last_den"] = g["DEN"].clone()
+        return g["last_den"], g["XN"].clone()
 
     def _split_outputs(self, out, b, st):
         """(uncond, cond) halves of the batched model output; uncond is None when CFG is off."""

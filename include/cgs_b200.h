@@ -215,6 +215,19 @@ int cgs_cfg_sampler_tail_fwd(const float* x, const void* out_uncond, const void*
                              float* denoised, float* x_next,
                              long long batch, long long per_sample, void* stream);
 
+/*
+ * cgs_cfg_sampler_tail_fwd with the step's sampler mode and coefficients read from device memory:
+ * step[0] = sampler mode (1, 2 or 3, stored as a float), step[1..4] = c0..c3. The launch is then identical for
+ * every step of a schedule, which lets the host replay one CUDA graph of the whole denoise step (UNet input ->
+ * UNet -> this kernel) instead of re-deriving the per-step Python scalars of comfy/k_diffusion/sampling.py:583-592.
+ * old_denoised must be a valid buffer (read only in mode 3).
+ */
+int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_uncond, const void* out_cond,
+                                 int out_is_bf16, const float* sigma, float cond_scale,
+                                 int pred_type, float sigma_data, const float* old_denoised,
+                                 const float* step, float* denoised, float* x_next,
+                                 long long batch, long long per_sample, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -194,6 +194,32 @@ def test_sampling_is_bitwise_reproducible():
     assert torch.equal(a, b)
 
 
+@pytest.mark.parametrize("golden,family,sampler,sched", [("e2e_tiny_sdxl_dpmpp2m", "tiny_sdxl", "dpmpp_2m", "karras"),
+                                                          ("e2e_tiny_sd15_euler", "tiny_sd15", "euler", "normal")])
+def test_cuda_graph_step_replay_equals_launch_by_launch(golden, family, sampler, sched):
+    """model_options["cuda_graph"]: the whole denoise step captured once and replayed (sampler coefficients read from
+    device memory) gives the same latents as launching it kernel by kernel, and our kernels are still accounted for."""
+    from comfy_gen_server_b200 import _native, sample as S
+    g = load_golden(golden)
+    seed = int(g["seed"])
+    patcher = _patcher(family, seed)
+    latent = torch.zeros(2, 4, 16, 16)
+    noise = S.prepare_noise(latent, seed)
+    extra = lambda k: {"pooled_output": g[k]} if k in g else {}
+    pos, neg = [[g["positive"], extra("pooled_pos")]], [[g["negative"], extra("pooled_neg")]]
+    outs, launches = [], []
+    for opt in (False, True, "auto"):
+        p2 = patcher.clone()
+        p2.model_options["cuda_graph"] = opt
+        _native.reset_launch_counters()
+        with torch.inference_mode():
+            outs.append(S.sample(p2, noise, 7, 7.0, sampler, sched, pos, neg, latent, seed=seed))
+        launches.append(sum(_native.LAUNCHES.values()))
+    assert torch.equal(outs[0], outs[1]), float((outs[0] - outs[1]).abs().max())
+    assert torch.equal(outs[0], outs[2])
+    assert launches[1] >= launches[0] - 2 and launches[0] > 0        # replays count the kernels they launch
+
+
 def test_channels_last_pipeline_matches_nchw_pipeline():
     """the NHWC end-to-end UNet (channels_last GroupNorm kernels, cuDNN NHWC convs, free token views)
     gives the same latents as the NCHW pipeline."""
