@@ -62,6 +62,12 @@ template <int NQT, int SPLIT> constexpr int kRegsSoftmax =
 #ifndef CGS_ATTN_POLY_PERIOD
 #define CGS_ATTN_POLY_PERIOD 4
 #endif
+#ifndef CGS_ATTN_WAITMODE            // how the service warps wait: 0 spin, 1 try_wait with suspend hint, 2 nanosleep
+#define CGS_ATTN_WAITMODE 1
+#endif
+#ifndef CGS_ATTN_EXPT                // timing experiments with wrong results (tools/attn_variants.py): 1 no exp2,
+#define CGS_ATTN_EXPT 0              // 2 no softmax arithmetic at all, 3 no row max
+#endif
 #ifndef CGS_ATTN_SPLIT               // threads per score row: 1 (thread == row) or 2 (half a row each; measured
 #define CGS_ATTN_SPLIT 1             // 4-5 % slower at every shape, kept for tools/attn_variants.py)
 #endif
@@ -202,12 +208,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             int stage = 0;
             uint32_t phase = 0;
             for (int j = 0; j < n_tiles; ++j) {
-                mbar_wait(&k_empty[stage], phase ^ 1);
+                mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_empty[stage], phase ^ 1);
                 mbar_expect_tx(&k_full[stage], NKB * TILE_BYTES);
                 for (int kb = 0; kb < NKB; ++kb)
                     tma_load_4d(smem + L::K_OFF + (stage * NKB + kb) * TILE_BYTES, &tmK,
                                 &k_full[stage], kb * 64, head, j * BLOCK_N, batch);
-                mbar_wait(&v_empty[stage], phase ^ 1);
+                mbar_wait_parked<CGS_ATTN_WAITMODE>(&v_empty[stage], phase ^ 1);
                 mbar_expect_tx(&v_full[stage], NKB * TILE_BYTES);
                 for (int kb = 0; kb < NKB; ++kb)
                     tma_load_4d(smem + L::V_OFF + (stage * NKB + kb) * TILE_BYTES, &tmV,
@@ -264,8 +270,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             };
 
             // prologue: S_t(0)
-            mbar_wait(&q_full[t], 0);
-            mbar_wait(&k_full[0], 0);
+            mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_full[t], 0);
+            mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[0], 0);
             tc_fence_after();
             issue_s(0, n_mma_of(0));
             tc_commit(&s_full[t]);
@@ -279,18 +285,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (nstage == KST) { nstage = 0; nphase ^= 1; }
                 if (j + 1 < n_tiles) {
                     // S(j+1): needs K(j+1) and the S buffer handed back (S(j) copied into registers)
-                    mbar_wait(&k_full[nstage], nphase);
+                    mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[nstage], nphase);
                     CGS_TRACE(2 + t, j, 0);
-                    mbar_wait(&s_free[t], j & 1);
+                    mbar_wait_parked<CGS_ATTN_WAITMODE>(&s_free[t], j & 1);
                     tc_fence_after();
                     issue_s(nstage, n_mma_of(j + 1));
                     tc_commit(&s_full[t]);
                     tc_commit(&k_empty[nstage]);
                     CGS_TRACE(2 + t, j, 1);
                 }
-                mbar_wait(&v_full[stage], phase);
+                mbar_wait_parked<CGS_ATTN_WAITMODE>(&v_full[stage], phase);
                 CGS_TRACE(2 + t, j, 2);
-                mbar_wait(&p_full[t], j & 1);
+                mbar_wait_parked<CGS_ATTN_WAITMODE>(&p_full[t], j & 1);
                 CGS_TRACE(2 + t, j, 3);
                 tc_fence_after();
                 issue_pv(stage, n_mma_of(j), j > 0 ? 1u : 0u);
@@ -351,7 +357,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
             float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-            for (int i = 0; i < COLS; i += 8) {
+            for (int i = 0; i < ((CGS_ATTN_EXPT == 2 || CGS_ATTN_EXPT == 3) ? 8 : COLS); i += 8) {
                 mx0 = fmax3(mx0, __uint_as_float(sr[i + 0]), __uint_as_float(sr[i + 1]));
                 mx1 = fmax3(mx1, __uint_as_float(sr[i + 2]), __uint_as_float(sr[i + 3]));
                 mx2 = fmax3(mx2, __uint_as_float(sr[i + 4]), __uint_as_float(sr[i + 5]));
@@ -389,7 +395,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             for (int i = 0; i < COLS / 2; ++i) {
                 const uint64_t x2 = ffma2(pack_u32x2(sr[2 * i], sr[2 * i + 1]), scale2, negm2);
                 uint64_t e2;
-                if ((i % kPolyPeriod) < kPolyPairs) {
+                if (CGS_ATTN_EXPT == 1 || CGS_ATTN_EXPT == 2) {
+                    e2 = x2;            // timing experiment: no exponentials
+                } else if ((i % kPolyPeriod) < kPolyPairs) {
                     e2 = ex2_poly2(x2);
                 } else {
                     float lo, hi;
@@ -399,7 +407,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (i & 1) acc1 = fadd2(acc1, e2); else acc0 = fadd2(acc0, e2);
                 float elo, ehi;
                 unpack_f32x2(e2, elo, ehi);
-                pr[i] = pack_bf16x2(elo, ehi);
+                pr[i] = CGS_ATTN_EXPT == 2 ? sr[2 * i] : pack_bf16x2(elo, ehi);
             }
             CGS_TRACE(t, j, 4);
             {

@@ -46,14 +46,11 @@ def timeit(step, warm=3, n=6):
             step(i)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t_cpu0 = time.perf_counter()
         e0.record()
         for i in range(n):
             step(warm + i)
         e1.record()
-        t_enq = time.perf_counter()
         torch.cuda.synchronize()
-        timeit.enqueue_ms = (t_enq - t_cpu0) * 1e3 / n     # host time to enqueue one step (GPU-bound if < GPU time)
     return e0.elapsed_time(e1) / n
 
 
@@ -74,8 +71,7 @@ def main():
         else:
             ms = timeit(step)
         out[v] = ms
-        print(json.dumps({"variant": v, "ms_per_step": ms, "images_per_s": 8 / (30 * ms / 1e3),
-                          "host_enqueue_ms_per_step": getattr(timeit, "enqueue_ms", None)}), flush=True)
+        print(json.dumps({"variant": v, "ms_per_step": ms, "images_per_s": 8 / (30 * ms / 1e3)}), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(out, open(os.path.join(ROOT, "gpurun_out", "step_variants.json"), "w"))
 
