@@ -506,11 +506,12 @@ class CFGGuider:
         tables = st["tables"]
         sigma_f = float(sigma_hat)
         st["calls"] += 1
-        if st["graph"] is None and st["calls"] >= 2:
+        if st["graph"] is None and st["calls"] >= 3:
             st["graph"] = self._maybe_capture_step(st, x, model_options)
         if st["graph"]:
             return self._graph_step(st, x, i, sigma_f, sampler, c0, c1, c2, c3, old_denoised)
-        probe = st["calls"] == 1 and st["graph_opt"] == "auto"
+        # (the first step also pays one-time costs -- cross-attention K/V, cuDNN plan selection -- so the second is probed)
+        probe = st["calls"] == 2 and st["graph_opt"] == "auto"
         if probe:
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()
