@@ -42,20 +42,19 @@ namespace cgs {
 
 namespace attn {
 constexpr int BLOCK_M = 128;
-constexpr int BLOCK_N = 128;
-constexpr int TILE_BYTES = 128 * 128;  // one [128 rows x 64 bf16] swizzled box
+constexpr int TILE_BYTES = 128 * 128;  // one [128 rows x 64 bf16] swizzled box (a Q tile; a 128-key K or V tile)
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
 #ifndef CGS_ATTN_SETMAXNREG
 #define CGS_ATTN_SETMAXNREG 1
 #endif
-// 4 * SPLIT softmax warps per query tile + one service warpgroup (TMA producer, one MMA issuer per tile, filler)
-template <int NQT, int SPLIT> constexpr int kThreads = (NQT * 4 * SPLIT + 4) * 32;
+// 4 softmax warps per query tile + one service warpgroup (TMA producer, one MMA issuer per tile, filler)
+template <int NQT> constexpr int kThreads = (NQT * 4 + 4) * 32;
 constexpr int kRegsService = 40;
 // registers per softmax thread after the hand-over: what the launch gives every thread (64 K / threads per SM,
 // rounded down to 8) times all threads, minus the service warpgroup's share, over the softmax threads
-template <int NQT, int SPLIT> constexpr int kRegsLaunch = (65536 / (kThreads<NQT, SPLIT> * (NQT == 1 ? 2 : 1))) / 8 * 8;
-template <int NQT, int SPLIT> constexpr int kRegsSoftmax =
-    ((kRegsLaunch<NQT, SPLIT> * kThreads<NQT, SPLIT> - 128 * kRegsService) / (kThreads<NQT, SPLIT> - 128)) / 8 * 8;
+template <int NQT> constexpr int kRegsLaunch = (65536 / (kThreads<NQT> * (NQT == 1 ? 2 : 1))) / 8 * 8;
+template <int NQT> constexpr int kRegsSoftmax =
+    ((kRegsLaunch<NQT> * kThreads<NQT> - 128 * kRegsService) / (kThreads<NQT> - 128)) / 8 * 8;
 #ifndef CGS_ATTN_POLY_PAIRS          // tuning overrides for tools/attn_variants.py
 #define CGS_ATTN_POLY_PAIRS 1
 #endif
@@ -67,9 +66,6 @@ template <int NQT, int SPLIT> constexpr int kRegsSoftmax =
 #endif
 #ifndef CGS_ATTN_EXPT                // timing experiments with wrong results (tools/attn_variants.py): 1 no exp2,
 #define CGS_ATTN_EXPT 0              // 2 no softmax arithmetic at all, 3 no row max
-#endif
-#ifndef CGS_ATTN_SPLIT               // threads per score row: 1 (thread == row) or 2 (half a row each; measured
-#define CGS_ATTN_SPLIT 1             // 4-5 % slower at every shape, kept for tools/attn_variants.py)
 #endif
 constexpr int kPolyPairs = CGS_ATTN_POLY_PAIRS;    // of every kPolyPeriod element pairs, this many use the FMA-pipe exp2
 constexpr int kPolyPeriod = CGS_ATTN_POLY_PERIOD;
@@ -106,23 +102,25 @@ struct AttnParams {
     } while (0)
 #endif
 
-template <int NKB, int NQT, int KST, int SPLIT>
+template <int NKB, int NQT, int KST, int BN>
 struct AttnSmem {
+    static constexpr int KV_TILE = BN * 128;          // one [BN keys x 64 bf16] swizzled box
     static constexpr int Q_OFF = 0;
     static constexpr int K_OFF = Q_OFF + NQT * NKB * attn::TILE_BYTES;
-    static constexpr int V_OFF = K_OFF + KST * NKB * attn::TILE_BYTES;
-    static constexpr int BAR_OFF = V_OFF + KST * NKB * attn::TILE_BYTES;
+    static constexpr int V_OFF = K_OFF + KST * NKB * KV_TILE;
+    static constexpr int BAR_OFF = V_OFF + KST * NKB * KV_TILE;
     static constexpr int NBARS = 5 * NQT + 4 * KST;
-    static constexpr int XCH_OFF = BAR_OFF + NBARS * 8 + 16;          // float [NQT][2 (parity)][SPLIT][128]
-    static constexpr int BYTES = XCH_OFF + (SPLIT > 1 ? NQT * 2 * SPLIT * 128 * 4 : 0) + 1024;
+    static constexpr int BYTES = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
-template <int NKB, int NQT, int KST, int SPLIT>
-__global__ void __launch_bounds__(attn::kThreads<NQT, SPLIT>, (NQT == 1 ? 2 : 1))
+template <int NKB, int NQT, int KST, int BN>
+__global__ void __launch_bounds__(attn::kThreads<NQT>, (NQT == 1 ? 2 : 1))
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
     using namespace attn;
-    using L = AttnSmem<NKB, NQT, KST, SPLIT>;
+    using L = AttnSmem<NKB, NQT, KST, BN>;
+    constexpr int BLOCK_N = BN;
+    constexpr int KV_TILE = L::KV_TILE;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
@@ -141,7 +139,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     CGS_TRACE_CTA(0);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    constexpr int PRODUCER_WARP = NQT * 4 * SPLIT;
+    constexpr int PRODUCER_WARP = NQT * 4;
     constexpr int MMA_WARP = PRODUCER_WARP + 1;      // first of NQT issuer warps
 
     const int q0 = blockIdx.x * (BLOCK_M * NQT);
@@ -152,8 +150,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int dv_n = ksteps_d << 4;           // N of the PV MMA (d rounded up to 16)
 
     constexpr uint32_t S_COL = 0;                 // S_t at t*128
-    constexpr uint32_t P_COL = NQT * BLOCK_N;     // P_t (bf16, 2 per column) at P_COL + t*64
-    constexpr uint32_t O_COL = NQT * 192;         // O_t at O_COL + t*dv_n
+    constexpr uint32_t P_COL = NQT * BLOCK_N;                     // P_t (bf16, 2 per column) at P_COL + t * BLOCK_N / 2
+    constexpr uint32_t O_COL = NQT * (BLOCK_N + BLOCK_N / 2);     // O_t at O_COL + t * dv_n
     const uint32_t o_stride = dv_n;
 
     if (warp == PRODUCER_WARP && elect_one()) {
@@ -166,9 +164,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             for (int t = 0; t < NQT; ++t) {
                 mbar_init(&q_full[t], 1);
                 mbar_init(&s_full[t], 1);
-                mbar_init(&p_full[t], 128 * SPLIT);
+                mbar_init(&p_full[t], 128);
                 mbar_init(&o_full[t], 1);
-                mbar_init(&s_free[t], 128 * SPLIT);
+                mbar_init(&s_free[t], 128);
             }
             for (int s = 0; s < KST; ++s) {
                 mbar_init(&k_full[s], 1);
@@ -209,14 +207,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             uint32_t phase = 0;
             for (int j = 0; j < n_tiles; ++j) {
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_empty[stage], phase ^ 1);
-                mbar_expect_tx(&k_full[stage], NKB * TILE_BYTES);
+                mbar_expect_tx(&k_full[stage], NKB * KV_TILE);
                 for (int kb = 0; kb < NKB; ++kb)
-                    tma_load_4d(smem + L::K_OFF + (stage * NKB + kb) * TILE_BYTES, &tmK,
+                    tma_load_4d(smem + L::K_OFF + (stage * NKB + kb) * KV_TILE, &tmK,
                                 &k_full[stage], kb * 64, head, j * BLOCK_N, batch);
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&v_empty[stage], phase ^ 1);
-                mbar_expect_tx(&v_full[stage], NKB * TILE_BYTES);
+                mbar_expect_tx(&v_full[stage], NKB * KV_TILE);
                 for (int kb = 0; kb < NKB; ++kb)
-                    tma_load_4d(smem + L::V_OFF + (stage * NKB + kb) * TILE_BYTES, &tmV,
+                    tma_load_4d(smem + L::V_OFF + (stage * NKB + kb) * KV_TILE, &tmV,
                                 &v_full[stage], kb * 64, head, j * BLOCK_N, batch);
                 if (++stage == KST) { stage = 0; phase ^= 1; }
             }
@@ -230,15 +228,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const uint32_t idesc_o = umma_idesc_bf16(BLOCK_M, dv_n, 1);
             // descriptor halves: K-major operands (Q, K): LBO 16 B, SBO 1024 B; MN-major V: LBO = one TMA box
             const uint64_t dk = umma_desc_sw128(0, 16, 1024);
-            const uint64_t dvv = umma_desc_sw128(0, TILE_BYTES, 1024);
+            const uint64_t dvv = umma_desc_sw128(0, KV_TILE, 1024);
             const uint32_t hi_k = static_cast<uint32_t>(dk >> 32), hi_v = static_cast<uint32_t>(dvv >> 32);
             // low word = start address >> 4 in bits [0,14) and the leading-dimension byte offset >> 4 in bits [16,30)
             const uint32_t q_lo = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::Q_OFF + t * NKB * TILE_BYTES) & 0x3FFFF) >> 4);
             const uint32_t k_lo0 = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::K_OFF) & 0x3FFFF) >> 4);
             const uint32_t v_lo0 = static_cast<uint32_t>(dvv) | ((smem_u32(smem + L::V_OFF) & 0x3FFFF) >> 4);
-            constexpr uint32_t STAGE_LO = (NKB * TILE_BYTES) >> 4;
+            constexpr uint32_t STAGE_LO = (NKB * KV_TILE) >> 4;
             const uint32_t s_tmem = tmem_base + S_COL + t * BLOCK_N;
-            const uint32_t p_tmem = tmem_base + P_COL + t * 64;
+            const uint32_t p_tmem = tmem_base + P_COL + t * (BLOCK_N / 2);
             const uint32_t o_tmem = tmem_base + O_COL + t * o_stride;
             auto n_mma_of = [&](int j) {
                 const int valid = min(BLOCK_N, p.Nk - j * BLOCK_N);
@@ -250,9 +248,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
                 for (int s = 0; s < NKB * 4; ++s) {
                     if (s < ksteps_d) {
-                        // 64-wide block kb = s / 4 (one TMA box, TILE_BYTES apart), 32 bytes per k-step inside it
-                        const uint32_t off = (s >> 2) * (TILE_BYTES >> 4) + (s & 3) * 2;
-                        umma_ss_lh(s_tmem, q_lo + off, hi_k, k_lo + off, hi_k, idesc_s, s != 0);
+                        // 64-wide block kb = s / 4 (one TMA box further on), 32 bytes per k-step inside it
+                        const uint32_t off_q = (s >> 2) * (TILE_BYTES >> 4) + (s & 3) * 2;
+                        const uint32_t off_k = (s >> 2) * (KV_TILE >> 4) + (s & 3) * 2;
+                        umma_ss_lh(s_tmem, q_lo + off_q, hi_k, k_lo + off_k, hi_k, idesc_s, s != 0);
                     }
                 }
             };
@@ -260,7 +259,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 const uint32_t v_lo = v_lo0 + stage * STAGE_LO;
                 const int ksteps = n_mma >> 4;
 #pragma unroll
-                for (int ks = 0; ks < 8; ++ks) {
+                for (int ks = 0; ks < BLOCK_N / 16; ++ks) {
                     if (ks < ksteps) {
                         // 16 key rows per step = 2 swizzle groups of 8 rows = 2048 bytes
                         umma_ts_lh(o_tmem, p_tmem + ks * 8, v_lo + ks * (2048 >> 4), hi_v, idesc_o,
@@ -311,25 +310,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
     } else {
         // ------------------------------------------------------------------ softmax warps
-        // SPLIT threads share a score row (COLS columns each). ncu on thread == row (two softmax warps per
-        // scheduler): issue active 51 %, XU 54 %, FMA 36 %, ALU 31 %, tensor 35 %; per warp and key tile ~745 issue
-        // cycles + ~800 cycles of fixed two-cycle stalls of the packed / half-rate instructions. Doubling the warps
-        // (SPLIT = 2) does not fill those slots: it measured 4-5 % slower.
+        // thread == query row. ncu with two softmax warps per scheduler (NQT = 2, 128 keys): issue active 51 %, XU
+        // 54 %, FMA 36 %, ALU 31 %, tensor 35 %: nothing saturated, the TMEM / barrier latencies of a tile are only
+        // covered by the one other warp. (Half a row per thread -- 4 warps per scheduler but still two phases --
+        // measured 4-5 % slower.)
 #if CGS_ATTN_SETMAXNREG
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(attn::kRegsSoftmax<NQT, SPLIT>));
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(attn::kRegsSoftmax<NQT>));
 #endif
-        constexpr int COLS = BLOCK_N / SPLIT;
-        const int t = warp / (4 * SPLIT);
-        const int h = (warp >> 2) % SPLIT;          // which column part of the row
+        constexpr int COLS = BLOCK_N;
+        const int t = warp >> 2;
         const int quad = warp & 3;
         const int row_in_tile = quad * 32 + lane;
         const uint32_t lane_field = static_cast<uint32_t>(quad * 32) << 16;
-        const uint32_t s_addr = tmem_base + lane_field + S_COL + t * BLOCK_N + h * COLS;
-        const uint32_t p_addr = tmem_base + lane_field + P_COL + t * 64 + h * (COLS / 2);
+        const uint32_t s_addr = tmem_base + lane_field + S_COL + t * BLOCK_N;
+        const uint32_t p_addr = tmem_base + lane_field + P_COL + t * (BLOCK_N / 2);
         const uint32_t o_addr = tmem_base + lane_field + O_COL + t * o_stride;
-        float* xch = reinterpret_cast<float*>(smem + L::XCH_OFF) + t * 2 * SPLIT * 128;
 
-        const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && quad == 0 && lane == 0 && h == 0;
+        const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && quad == 0 && lane == 0;
         float m_run = -INFINITY;  // running max, already multiplied by scale_log2
         float l_run = 0.f;        // this thread's part of the row sum
         const float scale = p.scale_log2;
@@ -349,7 +346,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             mbar_arrive(&s_free[t]);
             CGS_TRACE(t, j, 2);
 
-            const int n_valid = p.Nk - j * BLOCK_N - h * COLS;
+            const int n_valid = p.Nk - j * BLOCK_N;
             if (n_valid < COLS) {
 #pragma unroll
                 for (int i = 0; i < COLS; ++i)
@@ -364,15 +361,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 mx3 = fmax3(mx3, __uint_as_float(sr[i + 6]), __uint_as_float(sr[i + 7]));
             }
             float mx = fmaxf(fmax3(mx0, mx1, mx2), mx3);
-            if constexpr (SPLIT > 1) {
-                // agree on the row max with the thread(s) holding the other columns (double-buffered by key-tile
-                // parity: the barrier of tile j+1 orders every read of tile j before the writes of tile j+2)
-                float* slot = xch + (j & 1) * SPLIT * 128;
-                slot[h * 128 + row_in_tile] = mx;
-                named_bar_sync(1 + t, 128 * SPLIT);
-#pragma unroll
-                for (int o = 1; o < SPLIT; ++o) mx = fmaxf(mx, slot[((h + o) % SPLIT) * 128 + row_in_tile]);
-            }
             const float m_new = mx * scale;
 
             float alpha = 1.f;
@@ -425,7 +413,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
             for (int c = 0; c < COLS / 2; c += 32) tmem_st_x32(p_addr + c, pr + c);
             if (__any_sync(0xffffffffu, need_rescale)) {
-                for (int c = h; c < (dv_n >> 4); c += SPLIT) {      // the row's threads take alternate 16-column chunks
+                for (int c = 0; c < (dv_n >> 4); ++c) {
                     uint32_t orr[16];
                     tmem_ld_x16(o_addr + c * 16, orr);
                     tmem_wait_ld();
@@ -441,16 +429,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             CGS_TRACE(t, j, 5);
         }
 
-        if constexpr (SPLIT > 1) {
-            // whole-row sum: one more exchange (parity slot of a tile that does not exist)
-            float* slot = xch + (n_tiles & 1) * SPLIT * 128;
-            slot[h * 128 + row_in_tile] = l_run;
-            named_bar_sync(1 + t, 128 * SPLIT);
-#pragma unroll
-            for (int o = 1; o < SPLIT; ++o) l_run += slot[((h + o) % SPLIT) * 128 + row_in_tile];
-        }
-
-        // epilogue: O / l -> bf16 -> global (the row's threads take alternate 16-column chunks)
+        // epilogue: O / l -> bf16 -> global
         mbar_wait(&o_full[t], (n_tiles - 1) & 1);
         tc_fence_after();
         CGS_TRACE_CTA(2);
@@ -458,7 +437,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int q_row = q0 + t * BLOCK_M + row_in_tile;
         __nv_bfloat16* orow = p.out + (long long)batch * p.o_stride_b +
                               (long long)q_row * p.o_stride_n + (long long)head * p.o_stride_h;
-        for (int c = h; c < (dv_n >> 4); c += SPLIT) {
+        for (int c = 0; c < (dv_n >> 4); ++c) {
             uint32_t orr[16];
             tmem_ld_x16(o_addr + c * 16, orr);
             tmem_wait_ld();
@@ -486,23 +465,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
-template <int NKB, int NQT, int KST, int SPLIT = CGS_ATTN_SPLIT>
+template <int NKB, int NQT, int KST, int BN = 128>
 static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                        const AttnParams& p, cudaStream_t stream) {
-    using L = AttnSmem<NKB, NQT, KST, SPLIT>;
-    auto kern = attn_fwd_kernel<NKB, NQT, KST, SPLIT>;
+    using L = AttnSmem<NKB, NQT, KST, BN>;
+    auto kern = attn_fwd_kernel<NKB, NQT, KST, BN>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
     dim3 grid((p.Nq + attn::BLOCK_M * NQT - 1) / (attn::BLOCK_M * NQT), p.H, p.B);
-    kern<<<grid, attn::kThreads<NQT, SPLIT>, L::BYTES, stream>>>(tq, tk, tv, p);
+    kern<<<grid, attn::kThreads<NQT>, L::BYTES, stream>>>(tq, tk, tv, p);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }
 
 static int make_qkv_map(CUtensorMap* m, const void* ptr, int B, int N, int H, int d,
-                        long long sb, long long sn, long long sh) {
+                        long long sb, long long sn, long long sh, int box_rows = 128) {
     const uint64_t dims[4] = {(uint64_t)d, (uint64_t)H, (uint64_t)N, (uint64_t)B};
     const uint64_t strides[3] = {(uint64_t)sh * 2, (uint64_t)sn * 2, (uint64_t)sb * 2};
-    const uint32_t box[4] = {64, 1, 128, 1};
+    const uint32_t box[4] = {64, 1, (uint32_t)box_rows, 1};
     return make_tmap_bf16(m, ptr, 4, dims, strides, box);
 }
 
@@ -537,12 +516,6 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
         set_last_error("attention: output strides/pointer must be 16-byte aligned");
         return kBadArgument;
     }
-    CUtensorMap tq, tk, tv;
-    int rc;
-    if ((rc = make_qkv_map(&tq, q, B, Nq, H, d, q_stride_b, q_stride_n, q_stride_h)) != kOk) return rc;
-    if ((rc = make_qkv_map(&tk, k, B, Nk, H, d, k_stride_b, k_stride_n, k_stride_h)) != kOk) return rc;
-    if ((rc = make_qkv_map(&tv, v, B, Nk, H, d, v_stride_b, v_stride_n, v_stride_h)) != kOk) return rc;
-
     AttnParams p;
     p.dbg = nullptr;
     if (const char* e = getenv("CGS_ATTN_TRACE")) p.dbg = reinterpret_cast<long long*>(strtoull(e, nullptr, 0));
@@ -554,24 +527,33 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     p.scale_log2 = softmax_scale * 1.4426950408889634f;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int dv_n = ((d + 15) / 16) * 16;
-    const int n_tiles = (Nk + attn::BLOCK_N - 1) / attn::BLOCK_N;
-    // Two query tiles per CTA (ping-pong) for long key sequences; one tile per CTA with a single K/V
-    // stage for short ones (text cross-attention, tiny levels): small SMEM/TMEM footprint, 2 CTAs per SM.
-    // (up to 8 key tiles the set-up and epilogue of a CTA are a quarter of its life; two small CTAs per SM hide them)
-    bool two_tiles = Nq > attn::BLOCK_M && n_tiles > 8 && 2 * (192 + dv_n) <= 512;
-    if (const char* e = getenv("CGS_ATTN_MAX_TILES_1CTA")) {     // experiment knob: one query tile per CTA up to this many key tiles
-        if (n_tiles <= atoi(e)) two_tiles = false;
-    }
-    const int nqt = two_tiles ? 2 : 1;
+    const int n_tiles = (Nk + 127) / 128;
+    // Long key sequences at d <= 64: three query tiles per CTA against 64-key tiles (TMEM 3 x (64 S + 32 P + 64 O)
+    // = 480 columns), so every scheduler has three softmax warps in three different phases to cover the TMEM and
+    // barrier latencies of one another. d <= 128: two query tiles against 128-key tiles. Short key sequences (text
+    // cross-attention, up to 8 key tiles): one tile per CTA, 256 TMEM columns, two CTAs per SM, so the set-up and
+    // epilogue of one CTA overlap the loop of the other.
+    int max_1cta = 8;
+    if (const char* e = getenv("CGS_ATTN_MAX_TILES_1CTA")) max_1cta = atoi(e);   // experiment knob
+    const bool multi = Nq > attn::BLOCK_M && n_tiles > max_1cta;
+    int nqt = 1, bn = 128;
+    if (multi && d <= 64 && !getenv("CGS_ATTN_NO_3TILE")) { nqt = 3; bn = 64; }
+    else if (multi && 2 * (192 + dv_n) <= 512) { nqt = 2; }
     int cols = 32;
-    while (cols < nqt * (192 + dv_n)) cols *= 2;
+    while (cols < nqt * (bn + bn / 2 + dv_n)) cols *= 2;
     p.tmem_cols = cols;
+    CUtensorMap tq, tk, tv;
+    int rc;
+    if ((rc = make_qkv_map(&tq, q, B, Nq, H, d, q_stride_b, q_stride_n, q_stride_h)) != kOk) return rc;
+    if ((rc = make_qkv_map(&tk, k, B, Nk, H, d, k_stride_b, k_stride_n, k_stride_h, bn)) != kOk) return rc;
+    if ((rc = make_qkv_map(&tv, v, B, Nk, H, d, v_stride_b, v_stride_n, v_stride_h, bn)) != kOk) return rc;
     if (d <= 64) {
-        if (two_tiles) return launch_attn<1, 2, 3>(tq, tk, tv, p, st);
+        if (nqt == 3) return launch_attn<1, 3, 4, 64>(tq, tk, tv, p, st);
+        if (nqt == 2) return launch_attn<1, 2, 3>(tq, tk, tv, p, st);
         return n_tiles > 2 ? launch_attn<1, 1, 2>(tq, tk, tv, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, p, st);
     }
     if (d <= 128) {
-        if (two_tiles) return launch_attn<2, 2, 2>(tq, tk, tv, p, st);
+        if (nqt == 2) return launch_attn<2, 2, 2>(tq, tk, tv, p, st);
         return n_tiles > 2 ? launch_attn<2, 1, 2>(tq, tk, tv, p, st) : launch_attn<2, 1, 1>(tq, tk, tv, p, st);
     }
     return launch_attn<3, 1, 1>(tq, tk, tv, p, st);
