@@ -65,7 +65,7 @@ template <int NQT> constexpr int kRegsSoftmax =
 #define CGS_ATTN_WAITMODE 1
 #endif
 #ifndef CGS_ATTN_EXPT                // timing experiments with wrong results (tools/attn_variants.py): 1 no exp2,
-#define CGS_ATTN_EXPT 0              // 2 no softmax arithmetic at all, 3 no row max
+#define CGS_ATTN_EXPT 0              // 2 no softmax arithmetic at all, 3 no row max, 4 no output stores
 #endif
 constexpr int kPolyPairs = CGS_ATTN_POLY_PAIRS;    // of every kPolyPeriod element pairs, this many use the FMA-pipe exp2
 constexpr int kPolyPeriod = CGS_ATTN_POLY_PERIOD;
@@ -108,15 +108,16 @@ struct AttnSmem {
     static constexpr int Q_OFF = 0;
     static constexpr int K_OFF = Q_OFF + NQT * NKB * attn::TILE_BYTES;
     static constexpr int V_OFF = K_OFF + KST * NKB * KV_TILE;
-    static constexpr int BAR_OFF = V_OFF + KST * NKB * KV_TILE;
-    static constexpr int NBARS = 5 * NQT + 4 * KST;
+    static constexpr int O_OFF = V_OFF + KST * NKB * KV_TILE;      // one [128 rows x 64 bf16] output staging box per query tile
+    static constexpr int BAR_OFF = O_OFF + (NQT == 1 ? attn::TILE_BYTES : 0);   // (only the one-tile variants stage their output)
+    static constexpr int NBARS = 6 * NQT + 4 * KST;
     static constexpr int BYTES = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
 template <int NKB, int NQT, int KST, int BN>
 __global__ void __launch_bounds__(attn::kThreads<NQT>, (NQT == 1 ? 2 : 1))
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
     using namespace attn;
     using L = AttnSmem<NKB, NQT, KST, BN>;
     constexpr int BLOCK_N = BN;
@@ -130,7 +131,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint64_t* p_full = s_full + NQT;         // [NQT]
     uint64_t* o_full = p_full + NQT;         // [NQT]
     uint64_t* s_free = o_full + NQT;         // [NQT]
-    uint64_t* k_full = s_free + NQT;         // [KST]
+    uint64_t* q_empty = s_free + NQT;        // [NQT]
+    uint64_t* k_full = q_empty + NQT;        // [KST]
     uint64_t* k_empty = k_full + KST;        // [KST]
     uint64_t* v_full = k_empty + KST;        // [KST]
     uint64_t* v_empty = v_full + KST;        // [KST]
@@ -142,9 +144,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     constexpr int PRODUCER_WARP = NQT * 4;
     constexpr int MMA_WARP = PRODUCER_WARP + 1;      // first of NQT issuer warps
 
-    const int q0 = blockIdx.x * (BLOCK_M * NQT);
-    const int head = blockIdx.y;
-    const int batch = blockIdx.z;
+    // Persistent CTAs: work item w = (batch, head, block of NQT query tiles), query block fastest so that the CTAs
+    // working on one (batch, head) at the same time share its K/V in L2. Barriers, the K/V ring and the TMEM
+    // buffers carry over from one item to the next: Q(w+1), K/V(w+1) load and S(w+1) is computed while the
+    // softmax warps are still in the epilogue of w, and TMEM allocation / barrier set-up happen once per CTA.
+    // (Text cross-attention is one key tile per item: set-up + first-load latency + epilogue used to be 3/4 of a
+    // CTA's life.)
+    const int n_qblk = (p.Nq + BLOCK_M * NQT - 1) / (BLOCK_M * NQT);
+    const int n_items = n_qblk * p.H * p.B;
+    auto item_coords = [&](int w, int& q0, int& head, int& batch) {
+        const int qb = w % n_qblk;
+        const int r = w / n_qblk;
+        q0 = qb * (BLOCK_M * NQT);
+        head = r % p.H;
+        batch = r / p.H;
+    };
     const int n_tiles = (p.Nk + BLOCK_N - 1) / BLOCK_N;
     const int ksteps_d = (p.d + 15) >> 4;     // K steps of the QK^T MMA
     const int dv_n = ksteps_d << 4;           // N of the PV MMA (d rounded up to 16)
@@ -158,6 +172,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tma_prefetch_desc(&tmQ);
         tma_prefetch_desc(&tmK);
         tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmO);
     }
     if (warp == MMA_WARP) {
         if (elect_one()) {
@@ -167,6 +182,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 mbar_init(&p_full[t], 128);
                 mbar_init(&o_full[t], 1);
                 mbar_init(&s_free[t], 128);
+                mbar_init(&q_empty[t], 1);
             }
             for (int s = 0; s < KST; ++s) {
                 mbar_init(&k_full[s], 1);
@@ -197,14 +213,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (warp == PRODUCER_WARP) {
         // ------------------------------------------------------------------ TMA producer
         if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            uint32_t it = 0;                          // items done by this CTA
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+            int q0, head, batch;
+            item_coords(w, q0, head, batch);
             for (int t = 0; t < NQT; ++t) {
+                if (it > 0) mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_empty[t], (it - 1) & 1);   // S MMAs of the last item read Q
                 mbar_expect_tx(&q_full[t], NKB * TILE_BYTES);
                 for (int kb = 0; kb < NKB; ++kb)
                     tma_load_4d(smem + L::Q_OFF + (t * NKB + kb) * TILE_BYTES, &tmQ, &q_full[t],
                                 kb * 64, head, q0 + t * BLOCK_M, batch);
             }
-            int stage = 0;
-            uint32_t phase = 0;
             for (int j = 0; j < n_tiles; ++j) {
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_empty[stage], phase ^ 1);
                 mbar_expect_tx(&k_full[stage], NKB * KV_TILE);
@@ -218,13 +239,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                                 &v_full[stage], kb * 64, head, j * BLOCK_N, batch);
                 if (++stage == KST) { stage = 0; phase ^= 1; }
             }
+            }
         }
         __syncwarp();
     } else if (warp < MMA_WARP + NQT) {     // (the remaining warps only fill the service warpgroup up to four)
         // ------------------------------------------------------------------ MMA issuer for query tile t
         if (elect_one()) {
             const int t = warp - MMA_WARP;
-            const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+            const bool trace_me = blockIdx.x == 0;
             const uint32_t idesc_o = umma_idesc_bf16(BLOCK_M, dv_n, 1);
             // descriptor halves: K-major operands (Q, K): LBO 16 B, SBO 1024 B; MN-major V: LBO = one TMA box
             const uint64_t dk = umma_desc_sw128(0, 16, 1024);
@@ -268,17 +290,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 }
             };
 
-            // prologue: S_t(0)
-            mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_full[t], 0);
-            mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[0], 0);
-            tc_fence_after();
-            issue_s(0, n_mma_of(0));
-            tc_commit(&s_full[t]);
-            tc_commit(&k_empty[0]);
-
             int stage = 0;
             uint32_t phase = 0;
-            for (int j = 0; j < n_tiles; ++j) {
+            uint32_t g = 0;                           // key tiles done by this issuer (all items): barrier phases
+            uint32_t it = 0;
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+            // S of the item's first key tile: needs Q, K and (after the first item) the S buffer handed back
+            mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_full[t], it & 1);
+            mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[stage], phase);
+            if (g > 0) mbar_wait_parked<CGS_ATTN_WAITMODE>(&s_free[t], (g - 1) & 1);
+            tc_fence_after();
+            issue_s(stage, n_mma_of(0));
+            tc_commit(&s_full[t]);
+            tc_commit(&k_empty[stage]);
+            for (int j = 0; j < n_tiles; ++j, ++g) {
                 int nstage = stage + 1;
                 uint32_t nphase = phase;
                 if (nstage == KST) { nstage = 0; nphase ^= 1; }
@@ -286,16 +311,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     // S(j+1): needs K(j+1) and the S buffer handed back (S(j) copied into registers)
                     mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[nstage], nphase);
                     CGS_TRACE(2 + t, j, 0);
-                    mbar_wait_parked<CGS_ATTN_WAITMODE>(&s_free[t], j & 1);
+                    mbar_wait_parked<CGS_ATTN_WAITMODE>(&s_free[t], g & 1);
                     tc_fence_after();
                     issue_s(nstage, n_mma_of(j + 1));
                     tc_commit(&s_full[t]);
                     tc_commit(&k_empty[nstage]);
                     CGS_TRACE(2 + t, j, 1);
+                } else {
+                    tc_commit(&q_empty[t]);          // every S MMA of this item has been issued: Q may be replaced
                 }
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&v_full[stage], phase);
                 CGS_TRACE(2 + t, j, 2);
-                mbar_wait_parked<CGS_ATTN_WAITMODE>(&p_full[t], j & 1);
+                mbar_wait_parked<CGS_ATTN_WAITMODE>(&p_full[t], g & 1);
                 CGS_TRACE(2 + t, j, 3);
                 tc_fence_after();
                 issue_pv(stage, n_mma_of(j), j > 0 ? 1u : 0u);
@@ -304,6 +331,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 CGS_TRACE(2 + t, j, 4);
                 stage = nstage;
                 phase = nphase;
+            }
             }
         }
         __syncwarp();
@@ -326,15 +354,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const uint32_t p_addr = tmem_base + lane_field + P_COL + t * (BLOCK_N / 2);
         const uint32_t o_addr = tmem_base + lane_field + O_COL + t * o_stride;
 
-        const bool trace_me = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && quad == 0 && lane == 0;
-        float m_run = -INFINITY;  // running max, already multiplied by scale_log2
-        float l_run = 0.f;        // this thread's part of the row sum
+        const bool trace_me = blockIdx.x == 0 && quad == 0 && lane == 0;
         const float scale = p.scale_log2;
         const uint64_t scale2 = pack_f32x2(scale, scale);
+        uint32_t g = 0;           // key tiles done by this thread (all items): barrier phases
 
-        for (int j = 0; j < n_tiles; ++j) {
+        for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+        int q0, head, batch;
+        item_coords(w, q0, head, batch);
+        float m_run = -INFINITY;  // running max, already multiplied by scale_log2
+        float l_run = 0.f;        // row sum
+        for (int j = 0; j < n_tiles; ++j, ++g) {
             CGS_TRACE(t, j, 0);
-            mbar_wait(&s_full[t], j & 1);
+            mbar_wait(&s_full[t], g & 1);
             CGS_TRACE(t, j, 1);
             tc_fence_after();
             uint32_t sr[COLS];
@@ -404,10 +436,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 unpack_f32x2(acc1, s2, s3);
                 l_run += (s0 + s1) + (s2 + s3);
             }
-            if (j > 0) {
-                // PV(j-1) must have finished reading P(j-1) (and O must be quiescent for a rescale). It was issued
-                // a whole softmax ago, so this wait is normally already satisfied.
-                mbar_wait(&o_full[t], (j - 1) & 1);
+            if (g > 0) {
+                // PV of the previous key tile must have finished reading P (and O must be quiescent for a rescale).
+                // It was issued a whole softmax ago, so this wait is normally already satisfied.
+                mbar_wait(&o_full[t], (g - 1) & 1);
                 tc_fence_after();
             }
 #pragma unroll
@@ -429,11 +461,54 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             CGS_TRACE(t, j, 5);
         }
 
-        // epilogue: O / l -> bf16 -> global
-        mbar_wait(&o_full[t], (n_tiles - 1) & 1);
+        // epilogue: O / l -> bf16 -> global. (The next item's first PV, which overwrites O, is issued only after
+        // every thread of this warpgroup has arrived on p_full for it, i.e. after this epilogue.)
+        mbar_wait(&o_full[t], (g - 1) & 1);
         tc_fence_after();
         CGS_TRACE_CTA(2);
         const float inv_l = 1.f / l_run;
+        if constexpr (NQT == 1) {
+        // registers -> 128-byte-swizzled staging box -> one TMA store per 64-column block (row-strided 16-byte global
+        // stores from 128 threads cost a third of a cross-attention launch; the store clips ragged Nq and d < 64)
+        uint8_t* stage_row = smem + L::O_OFF + t * TILE_BYTES + row_in_tile * 128;
+        const int sw = row_in_tile & 7;
+        const bool store_leader = (quad == 0 && lane == 0);
+        for (int kb = 0; kb < NKB; ++kb) {
+            if (kb * 64 >= dv_n) break;
+            uint4 w[8];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint32_t orr[16];
+                if (kb * 64 + c * 16 < dv_n) {
+                    tmem_ld_x16(o_addr + kb * 64 + c * 16, orr);
+                    tmem_wait_ld();
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) orr[i] = 0u;
+                }
+                w[2 * c].x = pack_bf16x2(__uint_as_float(orr[0]) * inv_l, __uint_as_float(orr[1]) * inv_l);
+                w[2 * c].y = pack_bf16x2(__uint_as_float(orr[2]) * inv_l, __uint_as_float(orr[3]) * inv_l);
+                w[2 * c].z = pack_bf16x2(__uint_as_float(orr[4]) * inv_l, __uint_as_float(orr[5]) * inv_l);
+                w[2 * c].w = pack_bf16x2(__uint_as_float(orr[6]) * inv_l, __uint_as_float(orr[7]) * inv_l);
+                w[2 * c + 1].x = pack_bf16x2(__uint_as_float(orr[8]) * inv_l, __uint_as_float(orr[9]) * inv_l);
+                w[2 * c + 1].y = pack_bf16x2(__uint_as_float(orr[10]) * inv_l, __uint_as_float(orr[11]) * inv_l);
+                w[2 * c + 1].z = pack_bf16x2(__uint_as_float(orr[12]) * inv_l, __uint_as_float(orr[13]) * inv_l);
+                w[2 * c + 1].w = pack_bf16x2(__uint_as_float(orr[14]) * inv_l, __uint_as_float(orr[15]) * inv_l);
+            }
+            if (store_leader) tma_store_wait_read();          // the previous store has finished reading the box
+            named_bar_sync(1, 128);
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(stage_row + ((c ^ sw) << 4)) = w[c];
+            fence_proxy_async_smem();
+            named_bar_sync(1, 128);
+            if (store_leader && CGS_ATTN_EXPT != 4) {
+                tma_store_4d(&tmO, smem + L::O_OFF + t * TILE_BYTES, kb * 64, head, q0 + t * BLOCK_M, batch);
+                tma_store_commit();
+            }
+        }
+        } else {
+        // long key sequences: the epilogue is a per-mille of the item; plain 16-byte stores, no staging traffic
         const int q_row = q0 + t * BLOCK_M + row_in_tile;
         __nv_bfloat16* orow = p.out + (long long)batch * p.o_stride_b +
                               (long long)q_row * p.o_stride_n + (long long)head * p.o_stride_h;
@@ -441,7 +516,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             uint32_t orr[16];
             tmem_ld_x16(o_addr + c * 16, orr);
             tmem_wait_ld();
-            if (q_row < p.Nq) {
+            if (q_row < p.Nq && CGS_ATTN_EXPT != 4) {
                 uint4 w0, w1;
                 w0.x = pack_bf16x2(__uint_as_float(orr[0]) * inv_l, __uint_as_float(orr[1]) * inv_l);
                 w0.y = pack_bf16x2(__uint_as_float(orr[2]) * inv_l, __uint_as_float(orr[3]) * inv_l);
@@ -456,8 +531,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (c * 16 + 8 < p.d) dst[1] = w1;
             }
         }
+        }
         tc_fence_before();
         CGS_TRACE_CTA(3);
+        }
+        if (NQT == 1 && quad == 0 && lane == 0) tma_store_wait_all();     // shared memory must outlive the last store's reads
     }
 
     __syncthreads();
@@ -466,13 +544,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 }
 
 template <int NKB, int NQT, int KST, int BN = 128>
-static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
                        const AttnParams& p, cudaStream_t stream) {
     using L = AttnSmem<NKB, NQT, KST, BN>;
     auto kern = attn_fwd_kernel<NKB, NQT, KST, BN>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
-    dim3 grid((p.Nq + attn::BLOCK_M * NQT - 1) / (attn::BLOCK_M * NQT), p.H, p.B);
-    kern<<<grid, attn::kThreads<NQT>, L::BYTES, stream>>>(tq, tk, tv, p);
+    const long long items = (long long)((p.Nq + attn::BLOCK_M * NQT - 1) / (attn::BLOCK_M * NQT)) * p.H * p.B;
+    // one-tile variants: persistent CTAs (two per SM) walk the items; multi-tile variants: one CTA per item, handed
+    // out by the hardware scheduler (an item is tens of key tiles long, and static round-robin measured 3 % slower)
+    const long long resident = (long long)sm_count() * 2;
+    const unsigned grid = (unsigned)((NQT > 1 || items < resident) ? items : resident);
+    kern<<<grid, attn::kThreads<NQT>, L::BYTES, stream>>>(tq, tk, tv, to, p);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }
@@ -508,8 +590,8 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
         set_last_error("attention: head dim %d unsupported (multiple of 8, <= 192)", d);
         return kUnsupportedShape;
     }
-    if (H > 65535 || B > 65535) {
-        set_last_error("attention: H=%d / B=%d exceed the grid limits", H, B);
+    if ((long long)((Nq + 127) / 128) * H * B > 0x7fffffffLL) {
+        set_last_error("attention: too many (batch, head, query tile) work items");
         return kUnsupportedShape;
     }
     if ((o_stride_b | o_stride_n | o_stride_h) % 8 != 0 || (reinterpret_cast<uintptr_t>(out) & 0xF)) {
@@ -542,19 +624,20 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     int cols = 32;
     while (cols < nqt * (bn + bn / 2 + dv_n)) cols *= 2;
     p.tmem_cols = cols;
-    CUtensorMap tq, tk, tv;
+    CUtensorMap tq, tk, tv, to;
     int rc;
+    if ((rc = make_qkv_map(&to, out, B, Nq, H, d, o_stride_b, o_stride_n, o_stride_h)) != kOk) return rc;
     if ((rc = make_qkv_map(&tq, q, B, Nq, H, d, q_stride_b, q_stride_n, q_stride_h)) != kOk) return rc;
     if ((rc = make_qkv_map(&tk, k, B, Nk, H, d, k_stride_b, k_stride_n, k_stride_h, bn)) != kOk) return rc;
     if ((rc = make_qkv_map(&tv, v, B, Nk, H, d, v_stride_b, v_stride_n, v_stride_h, bn)) != kOk) return rc;
     if (d <= 64) {
-        if (nqt == 3) return launch_attn<1, 3, 4, 64>(tq, tk, tv, p, st);
-        if (nqt == 2) return launch_attn<1, 2, 3>(tq, tk, tv, p, st);
-        return n_tiles > 2 ? launch_attn<1, 1, 2>(tq, tk, tv, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, p, st);
+        if (nqt == 3) return launch_attn<1, 3, 4, 64>(tq, tk, tv, to, p, st);
+        if (nqt == 2) return launch_attn<1, 2, 3>(tq, tk, tv, to, p, st);
+        return n_tiles > 2 ? launch_attn<1, 1, 2>(tq, tk, tv, to, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, to, p, st);
     }
     if (d <= 128) {
-        if (nqt == 2) return launch_attn<2, 2, 2>(tq, tk, tv, p, st);
-        return n_tiles > 2 ? launch_attn<2, 1, 2>(tq, tk, tv, p, st) : launch_attn<2, 1, 1>(tq, tk, tv, p, st);
+        if (nqt == 2) return launch_attn<2, 2, 2>(tq, tk, tv, to, p, st);
+        return n_tiles > 2 ? launch_attn<2, 1, 2>(tq, tk, tv, to, p, st) : launch_attn<2, 1, 1>(tq, tk, tv, to, p, st);
     }
-    return launch_attn<3, 1, 1>(tq, tk, tv, p, st);
+    return launch_attn<3, 1, 1>(tq, tk, tv, to, p, st);
 }
