@@ -105,12 +105,15 @@ struct AttnParams {
 template <int NKB, int NQT, int KST, int BN>
 struct AttnSmem {
     static constexpr int KV_TILE = BN * 128;          // one [BN keys x 64 bf16] swizzled box
+    // one- or two-key-tile items (text cross-attention) are as long as one HBM round trip: two Q buffers, so that the
+    // query tile of the item after next is already on its way
+    static constexpr int QBUF = (NQT == 1 && NKB == 1 && KST == 1) ? 2 : 1;
     static constexpr int Q_OFF = 0;
-    static constexpr int K_OFF = Q_OFF + NQT * NKB * attn::TILE_BYTES;
+    static constexpr int K_OFF = Q_OFF + QBUF * NQT * NKB * attn::TILE_BYTES;
     static constexpr int V_OFF = K_OFF + KST * NKB * KV_TILE;
     static constexpr int O_OFF = V_OFF + KST * NKB * KV_TILE;      // one [128 rows x 64 bf16] output staging box per query tile
     static constexpr int BAR_OFF = O_OFF + (NQT == 1 ? attn::TILE_BYTES : 0);   // (only the one-tile variants stage their output)
-    static constexpr int NBARS = 6 * NQT + 4 * KST;
+    static constexpr int NBARS = (4 + 2 * QBUF) * NQT + 4 * KST;
     static constexpr int BYTES = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
@@ -126,13 +129,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
-    uint64_t* q_full = bars;                 // [NQT]
-    uint64_t* s_full = q_full + NQT;         // [NQT]
+    constexpr int QBUF = L::QBUF;
+    uint64_t* q_full = bars;                 // [QBUF * NQT]
+    uint64_t* s_full = q_full + QBUF * NQT;  // [NQT]
     uint64_t* p_full = s_full + NQT;         // [NQT]
     uint64_t* o_full = p_full + NQT;         // [NQT]
     uint64_t* s_free = o_full + NQT;         // [NQT]
-    uint64_t* q_empty = s_free + NQT;        // [NQT]
-    uint64_t* k_full = q_empty + NQT;        // [KST]
+    uint64_t* q_empty = s_free + NQT;        // [QBUF * NQT]
+    uint64_t* k_full = q_empty + QBUF * NQT; // [KST]
     uint64_t* k_empty = k_full + KST;        // [KST]
     uint64_t* v_full = k_empty + KST;        // [KST]
     uint64_t* v_empty = v_full + KST;        // [KST]
@@ -176,13 +180,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
     if (warp == MMA_WARP) {
         if (elect_one()) {
-            for (int t = 0; t < NQT; ++t) {
+            for (int t = 0; t < QBUF * NQT; ++t) {
                 mbar_init(&q_full[t], 1);
+                mbar_init(&q_empty[t], 1);
+            }
+            for (int t = 0; t < NQT; ++t) {
                 mbar_init(&s_full[t], 1);
                 mbar_init(&p_full[t], 128);
                 mbar_init(&o_full[t], 1);
                 mbar_init(&s_free[t], 128);
-                mbar_init(&q_empty[t], 1);
             }
             for (int s = 0; s < KST; ++s) {
                 mbar_init(&k_full[s], 1);
@@ -219,12 +225,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
             int q0, head, batch;
             item_coords(w, q0, head, batch);
+            const uint32_t qslot = it % QBUF, quse = it / QBUF;      // Q buffer of this item and how often it was used
             for (int t = 0; t < NQT; ++t) {
-                if (it > 0) mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_empty[t], (it - 1) & 1);   // S MMAs of the last item read Q
-                mbar_expect_tx(&q_full[t], NKB * TILE_BYTES);
+                // the S MMAs of the item that used this buffer last have read Q
+                if (quse > 0) mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_empty[qslot * NQT + t], (quse - 1) & 1);
+                mbar_expect_tx(&q_full[qslot * NQT + t], NKB * TILE_BYTES);
                 for (int kb = 0; kb < NKB; ++kb)
-                    tma_load_4d(smem + L::Q_OFF + (t * NKB + kb) * TILE_BYTES, &tmQ, &q_full[t],
-                                kb * 64, head, q0 + t * BLOCK_M, batch);
+                    tma_load_4d(smem + L::Q_OFF + ((qslot * NQT + t) * NKB + kb) * TILE_BYTES, &tmQ,
+                                &q_full[qslot * NQT + t], kb * 64, head, q0 + t * BLOCK_M, batch);
             }
             for (int j = 0; j < n_tiles; ++j) {
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_empty[stage], phase ^ 1);
@@ -253,7 +261,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const uint64_t dvv = umma_desc_sw128(0, KV_TILE, 1024);
             const uint32_t hi_k = static_cast<uint32_t>(dk >> 32), hi_v = static_cast<uint32_t>(dvv >> 32);
             // low word = start address >> 4 in bits [0,14) and the leading-dimension byte offset >> 4 in bits [16,30)
-            const uint32_t q_lo = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::Q_OFF + t * NKB * TILE_BYTES) & 0x3FFFF) >> 4);
+            const uint32_t q_lo0 = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::Q_OFF + t * NKB * TILE_BYTES) & 0x3FFFF) >> 4);
+            uint32_t q_lo = q_lo0;
             const uint32_t k_lo0 = static_cast<uint32_t>(dk) | ((smem_u32(smem + L::K_OFF) & 0x3FFFF) >> 4);
             const uint32_t v_lo0 = static_cast<uint32_t>(dvv) | ((smem_u32(smem + L::V_OFF) & 0x3FFFF) >> 4);
             constexpr uint32_t STAGE_LO = (NKB * KV_TILE) >> 4;
@@ -296,7 +305,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             uint32_t it = 0;
             for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
             // S of the item's first key tile: needs Q, K and (after the first item) the S buffer handed back
-            mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_full[t], it & 1);
+            const uint32_t qslot = it % QBUF, quse = it / QBUF;
+            q_lo = q_lo0 + qslot * ((NQT * NKB * TILE_BYTES) >> 4);
+            mbar_wait_parked<CGS_ATTN_WAITMODE>(&q_full[qslot * NQT + t], quse & 1);
             mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[stage], phase);
             if (g > 0) mbar_wait_parked<CGS_ATTN_WAITMODE>(&s_free[t], (g - 1) & 1);
             tc_fence_after();
@@ -310,25 +321,25 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (j + 1 < n_tiles) {
                     // S(j+1): needs K(j+1) and the S buffer handed back (S(j) copied into registers)
                     mbar_wait_parked<CGS_ATTN_WAITMODE>(&k_full[nstage], nphase);
-                    CGS_TRACE(2 + t, j, 0);
+                    CGS_TRACE(2 + t, g, 0);
                     mbar_wait_parked<CGS_ATTN_WAITMODE>(&s_free[t], g & 1);
                     tc_fence_after();
                     issue_s(nstage, n_mma_of(j + 1));
                     tc_commit(&s_full[t]);
                     tc_commit(&k_empty[nstage]);
-                    CGS_TRACE(2 + t, j, 1);
+                    CGS_TRACE(2 + t, g, 1);
                 } else {
-                    tc_commit(&q_empty[t]);          // every S MMA of this item has been issued: Q may be replaced
+                    tc_commit(&q_empty[(it % QBUF) * NQT + t]);   // every S MMA of this item has been issued: Q may be replaced
                 }
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&v_full[stage], phase);
-                CGS_TRACE(2 + t, j, 2);
+                CGS_TRACE(2 + t, g, 2);
                 mbar_wait_parked<CGS_ATTN_WAITMODE>(&p_full[t], g & 1);
-                CGS_TRACE(2 + t, j, 3);
+                CGS_TRACE(2 + t, g, 3);
                 tc_fence_after();
                 issue_pv(stage, n_mma_of(j), j > 0 ? 1u : 0u);
                 tc_commit(&o_full[t]);
                 tc_commit(&v_empty[stage]);
-                CGS_TRACE(2 + t, j, 4);
+                CGS_TRACE(2 + t, g, 4);
                 stage = nstage;
                 phase = nphase;
             }
@@ -365,9 +376,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         float m_run = -INFINITY;  // running max, already multiplied by scale_log2
         float l_run = 0.f;        // row sum
         for (int j = 0; j < n_tiles; ++j, ++g) {
-            CGS_TRACE(t, j, 0);
+            CGS_TRACE(t, g, 0);
             mbar_wait(&s_full[t], g & 1);
-            CGS_TRACE(t, j, 1);
+            CGS_TRACE(t, g, 1);
             tc_fence_after();
             uint32_t sr[COLS];
 #pragma unroll
@@ -376,7 +387,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // S(j) is in registers: give the buffer back so S(j+1) is computed during this softmax
             tc_fence_before();
             mbar_arrive(&s_free[t]);
-            CGS_TRACE(t, j, 2);
+            CGS_TRACE(t, g, 2);
 
             const int n_valid = p.Nk - j * BLOCK_N;
             if (n_valid < COLS) {
@@ -408,7 +419,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const uint64_t negm2 = pack_f32x2(-m_run, -m_run);
             uint32_t pr[COLS / 2];
             uint64_t acc0 = 0ull, acc1 = 0ull;   // two packed (lo, hi) partial row sums
-            CGS_TRACE(t, j, 3);
+            CGS_TRACE(t, g, 3);
             // x = s * scale - m (packed FFMA2); 2^x: the MUFU gives 16 lanes/clk/SM, so kPolyPairs of every
             // kPolyPeriod pairs go to a degree-3 polynomial on the FMA pipe; row sum (packed FADD2); bf16 pack
 #pragma unroll
@@ -429,7 +440,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 unpack_f32x2(e2, elo, ehi);
                 pr[i] = CGS_ATTN_EXPT == 2 ? sr[2 * i] : pack_bf16x2(elo, ehi);
             }
-            CGS_TRACE(t, j, 4);
+            CGS_TRACE(t, g, 4);
             {
                 float s0, s1, s2, s3;
                 unpack_f32x2(acc0, s0, s1);
@@ -458,7 +469,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(&p_full[t]);
-            CGS_TRACE(t, j, 5);
+            CGS_TRACE(t, g, 5);
         }
 
         // epilogue: O / l -> bf16 -> global. (The next item's first PV, which overwrites O, is issued only after
@@ -476,16 +487,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int kb = 0; kb < NKB; ++kb) {
             if (kb * 64 >= dv_n) break;
             uint4 w[8];
+            uint32_t oall[64];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                uint32_t orr[16];
                 if (kb * 64 + c * 16 < dv_n) {
-                    tmem_ld_x16(o_addr + kb * 64 + c * 16, orr);
-                    tmem_wait_ld();
+                    tmem_ld_x16(o_addr + kb * 64 + c * 16, oall + c * 16);
                 } else {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) orr[i] = 0u;
+                    for (int i = 0; i < 16; ++i) oall[c * 16 + i] = 0u;
                 }
+            }
+            tmem_wait_ld();
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint32_t* orr = oall + c * 16;
                 w[2 * c].x = pack_bf16x2(__uint_as_float(orr[0]) * inv_l, __uint_as_float(orr[1]) * inv_l);
                 w[2 * c].y = pack_bf16x2(__uint_as_float(orr[2]) * inv_l, __uint_as_float(orr[3]) * inv_l);
                 w[2 * c].z = pack_bf16x2(__uint_as_float(orr[4]) * inv_l, __uint_as_float(orr[5]) * inv_l);
