@@ -23,6 +23,8 @@ _c_float = ctypes.c_float
 # name -> argtypes; every function returns int. Must list every symbol of include/cgs_b200.h.
 _SIGNATURES = {
     "cgs_attention_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 12 + [_c_float, _c_void_p],
+    "cgs_attention_masked_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 12 + [_c_float, _c_void_p] + [_c_ll] * 3
+                                + [_c_void_p],
     "cgs_layernorm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_add_layernorm_fwd": [_c_void_p] * 6 + [_c_ll, _c_int, _c_float, _c_void_p],
     "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
@@ -152,8 +154,33 @@ def _require_cuda(name: str, t: torch.Tensor, dtype: torch.dtype) -> None:
 # ----------------------------------------------------------------------------------------------
 # attention
 # ----------------------------------------------------------------------------------------------
-def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> torch.Tensor:
-    """softmax(q k^T / sqrt(d)) v per head; q [B, Nq, heads*d], k/v [B, Nk, heads*d] -> [B, Nq, heads*d].
+def _additive_mask(mask: torch.Tensor, B: int, heads: int, Nq: int, Nk: int) -> torch.Tensor:
+    """The reference's mask forms as one fp32 additive [B, heads, Nq, Nk] view (0-strides where it broadcasts):
+    boolean keep-masks (True = attend) and float additive masks, 2-D [Nq, Nk], 3-D [bs, Nq, Nk] (attention.py:118-123)
+    or anything that broadcasts to [B, heads, Nq, Nk] (SDPA's attn_mask, attention.py:345)."""
+    m = mask
+    if m.dtype == torch.bool:
+        m = torch.where(m, 0.0, -1.0e30).to(torch.float32)
+    else:
+        m = m.to(torch.float32)
+    if m.dim() == 2:
+        m = m[None, None]
+    elif m.dim() == 3:
+        m = m[:, None]
+    elif m.dim() != 4:
+        raise RuntimeError(f"attention mask: unsupported rank {mask.dim()}")
+    try:
+        m = m.expand(B, heads, Nq, Nk)
+    except RuntimeError:
+        raise RuntimeError(f"attention mask {tuple(mask.shape)} does not broadcast to [{B}, {heads}, {Nq}, {Nk}]")
+    if m.stride(3) != 1:                    # the key dimension itself is broadcast: materialise rows
+        m = m.contiguous()
+    return m
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
+              mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """softmax(q k^T / sqrt(d) (+ mask)) v per head; q [B, Nq, heads*d], k/v [B, Nk, heads*d] -> [B, Nq, heads*d].
 
     Same layout contract as the reference's optimized_attention (attention.py:337-349). Inputs may
     be views with arbitrary batch/token strides (last dim contiguous), e.g. slices of a fused QKV.
@@ -170,6 +197,18 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> 
     d = inner // heads
     out = torch.empty((B, Nq, inner), dtype=torch.bfloat16, device=q.device)
     if B == 0 or Nq == 0:
+        return out
+    if mask is not None:
+        if not mask.is_cuda:
+            raise RuntimeError("attention mask: must be a CUDA tensor")
+        m = _additive_mask(mask, B, heads, Nq, Nk)
+        with _Launch("attention", q, 4.0 * B * heads * Nq * Nk * d):
+            rc = load_library().cgs_attention_masked_fwd(
+                q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, heads, Nq, Nk, d,
+                q.stride(0), q.stride(1), d, k.stride(0), k.stride(1), d, v.stride(0), v.stride(1), d,
+                out.stride(0), out.stride(1), d, float(d) ** -0.5, m.data_ptr(), m.stride(0), m.stride(1), m.stride(2),
+                _stream(q))
+        _check(rc, "cgs_attention_masked_fwd")
         return out
     with _Launch("attention", q, 4.0 * B * heads * Nq * Nk * d):
         rc = load_library().cgs_attention_fwd(

@@ -45,14 +45,11 @@ def _ver(t) -> int:
 # ----------------------------------------------------------------------------------------------
 def attention_b200(q, k, v, heads, mask=None):
     """Drop-in for attention_pytorch (attention.py:337-349): q [B, Nq, heads*d], k/v [B, Nk, heads*d]
-    -> [B, Nq, heads*d]; inputs are not modified. Runs cgs_attention_fwd; no SDPA, no fallback."""
-    if mask is not None:
-        raise NotImplementedError(
-            "attention_b200: attention masks are not supported by the B200 kernel (the UNet hot path "
-            "never passes one: attention.py:411-414, 520, 560)")
+    -> [B, Nq, heads*d]; inputs are not modified. Runs cgs_attention_fwd (cgs_attention_masked_fwd when a mask is
+    given: boolean keep-mask or additive float, attention.py:111-123); no SDPA, no fallback."""
     if q.dtype != torch.bfloat16:
         raise RuntimeError(f"attention_b200: bf16 CUDA tensors required, got {q.dtype} on {q.device}")
-    return _native.attention(q, k, v, heads)
+    return _native.attention(q, k, v, heads, mask)
 
 
 optimized_attention = attention_b200

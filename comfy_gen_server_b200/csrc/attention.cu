@@ -78,6 +78,10 @@ struct AttnParams {
     long long o_stride_b, o_stride_n, o_stride_h;  // elements
     int B, H, Nq, Nk, d;
     float scale_log2;
+    // optional additive mask (fp32, added to the scaled scores; key stride 1, 0-strides broadcast)
+    const float* mask;
+    long long mask_sb, mask_sh, mask_sq;   // elements
+    float inv_scale;                        // 1 / softmax_scale: S + mask * inv_scale == (S * scale + mask) / scale
 };
 
 // The timeline stamps split the softmax loop into basic blocks and keep ptxas from overlapping its phases, so they
@@ -117,7 +121,7 @@ struct AttnSmem {
     static constexpr int BYTES = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
-template <int NKB, int NQT, int KST, int BN>
+template <int NKB, int NQT, int KST, int BN, bool MASK>
 __global__ void __launch_bounds__(attn::kThreads<NQT>, (NQT == 1 ? 2 : 1))
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
@@ -374,6 +378,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         int q0, head, batch;
         item_coords(w, q0, head, batch);
         float m_run = -INFINITY;  // running max, already multiplied by scale_log2
+        float m_raw = -INFINITY;  // the same before scaling (used by the masked variant only)
         float l_run = 0.f;        // row sum
         for (int j = 0; j < n_tiles; ++j, ++g) {
             CGS_TRACE(t, g, 0);
@@ -390,6 +395,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             CGS_TRACE(t, g, 2);
 
             const int n_valid = p.Nk - j * BLOCK_N;
+            if constexpr (MASK) {
+                // optimized_attention_masked (attention.py:111-123 / SDPA attn_mask): scores * scale + mask. Not on
+                // the UNet's path (its mask is always None); one scalar load per score, no tuning.
+                const int q_row_m = min(q0 + t * BLOCK_M + row_in_tile, p.Nq - 1);
+                const float* mrow = p.mask + (long long)batch * p.mask_sb + (long long)head * p.mask_sh +
+                                    (long long)q_row_m * p.mask_sq + (long long)j * BLOCK_N;
+#pragma unroll 8
+                for (int i = 0; i < COLS; ++i)
+                    if (i < n_valid)
+                        sr[i] = __float_as_uint(fmaf(__ldg(mrow + i), p.inv_scale, __uint_as_float(sr[i])));
+            }
             if (n_valid < COLS) {
 #pragma unroll
                 for (int i = 0; i < COLS; ++i)
@@ -410,13 +426,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             bool need_rescale = false;
             if (j == 0) {
                 m_run = m_new;
+                m_raw = mx;
             } else if (m_new > m_run + kRescaleThreshold) {
                 alpha = ex2_approx(m_run - m_new);
                 l_run *= alpha;
                 m_run = m_new;
+                m_raw = mx;
                 need_rescale = true;
             }
             const uint64_t negm2 = pack_f32x2(-m_run, -m_run);
+            // masked variant: x = (s - m) * scale, subtraction first. With s * scale - m * scale in one FMA the
+            // rounding of m * scale (half an ulp of m) is left in x; harmless for |m| ~ 10, an overflow for a row
+            // whose keys are all masked (m ~ -1e30), which must come out as the uniform average of attention.py:113-117
+            const uint64_t negmr2 = pack_f32x2(-m_raw, -m_raw);
             uint32_t pr[COLS / 2];
             uint64_t acc0 = 0ull, acc1 = 0ull;   // two packed (lo, hi) partial row sums
             CGS_TRACE(t, g, 3);
@@ -424,7 +446,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // kPolyPeriod pairs go to a degree-3 polynomial on the FMA pipe; row sum (packed FADD2); bf16 pack
 #pragma unroll
             for (int i = 0; i < COLS / 2; ++i) {
-                const uint64_t x2 = ffma2(pack_u32x2(sr[2 * i], sr[2 * i + 1]), scale2, negm2);
+                const uint64_t s2 = pack_u32x2(sr[2 * i], sr[2 * i + 1]);
+                const uint64_t x2 = MASK ? ffma2(fadd2(s2, negmr2), scale2, 0ull) : ffma2(s2, scale2, negm2);
                 uint64_t e2;
                 if (CGS_ATTN_EXPT == 1 || CGS_ATTN_EXPT == 2) {
                     e2 = x2;            // timing experiment: no exponentials
@@ -558,11 +581,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
-template <int NKB, int NQT, int KST, int BN = 128>
+template <int NKB, int NQT, int KST, int BN = 128, bool MASK = false>
 static int launch_attn(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
                        const AttnParams& p, cudaStream_t stream) {
     using L = AttnSmem<NKB, NQT, KST, BN>;
-    auto kern = attn_fwd_kernel<NKB, NQT, KST, BN>;
+    auto kern = attn_fwd_kernel<NKB, NQT, KST, BN, MASK>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
     const long long items = (long long)((p.Nq + attn::BLOCK_M * NQT - 1) / (attn::BLOCK_M * NQT)) * p.H * p.B;
     // one-tile variants: persistent CTAs (two per SM) walk the items; multi-tile variants: one CTA per item, handed
@@ -582,16 +605,14 @@ static int make_qkv_map(CUtensorMap* m, const void* ptr, int B, int N, int H, in
     return make_tmap_bf16(m, ptr, 4, dims, strides, box);
 }
 
-}  // namespace cgs
-
-extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, void* out, int B,
-                                 int H, int Nq, int Nk, int d, long long q_stride_b,
-                                 long long q_stride_n, long long q_stride_h, long long k_stride_b,
-                                 long long k_stride_n, long long k_stride_h, long long v_stride_b,
-                                 long long v_stride_n, long long v_stride_h, long long o_stride_b,
-                                 long long o_stride_n, long long o_stride_h, float softmax_scale,
-                                 void* stream) {
-    using namespace cgs;
+static int attention_entry(const void* q, const void* k, const void* v, void* out, int B,
+                           int H, int Nq, int Nk, int d, long long q_stride_b,
+                           long long q_stride_n, long long q_stride_h, long long k_stride_b,
+                           long long k_stride_n, long long k_stride_h, long long v_stride_b,
+                           long long v_stride_n, long long v_stride_h, long long o_stride_b,
+                           long long o_stride_n, long long o_stride_h, float softmax_scale,
+                           const float* mask, long long mask_sb, long long mask_sh, long long mask_sq,
+                           void* stream) {
     if (B < 0 || H <= 0 || Nq < 0 || Nk < 0 || d <= 0) {
         set_last_error("attention: bad sizes B=%d H=%d Nq=%d Nk=%d d=%d", B, H, Nq, Nk, d);
         return kBadArgument;
@@ -622,6 +643,13 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     p.o_stride_h = o_stride_h;
     p.B = B; p.H = H; p.Nq = Nq; p.Nk = Nk; p.d = d;
     p.scale_log2 = softmax_scale * 1.4426950408889634f;
+    p.mask = mask;
+    p.mask_sb = mask_sb; p.mask_sh = mask_sh; p.mask_sq = mask_sq;
+    p.inv_scale = 1.0f / softmax_scale;
+    if (mask != nullptr && !(softmax_scale > 0.f)) {
+        set_last_error("attention: a mask needs a positive softmax scale");
+        return kBadArgument;
+    }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int dv_n = ((d + 15) / 16) * 16;
     const int n_tiles = (Nk + 127) / 128;
@@ -632,7 +660,7 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     // epilogue of one CTA overlap the loop of the other.
     int max_1cta = 8;
     if (const char* e = getenv("CGS_ATTN_MAX_TILES_1CTA")) max_1cta = atoi(e);   // experiment knob
-    const bool multi = Nq > attn::BLOCK_M && n_tiles > max_1cta;
+    const bool multi = Nq > attn::BLOCK_M && n_tiles > max_1cta && mask == nullptr;   // masked: one-tile variants only
     int nqt = 1, bn = 128;
     if (multi && d <= 64 && !getenv("CGS_ATTN_NO_3TILE")) { nqt = 3; bn = 64; }
     else if (multi && 2 * (192 + dv_n) <= 512) { nqt = 2; }
@@ -645,6 +673,13 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
     if ((rc = make_qkv_map(&tq, q, B, Nq, H, d, q_stride_b, q_stride_n, q_stride_h)) != kOk) return rc;
     if ((rc = make_qkv_map(&tk, k, B, Nk, H, d, k_stride_b, k_stride_n, k_stride_h, bn)) != kOk) return rc;
     if ((rc = make_qkv_map(&tv, v, B, Nk, H, d, v_stride_b, v_stride_n, v_stride_h, bn)) != kOk) return rc;
+    if (mask != nullptr) {
+        if (d <= 64) return n_tiles > 2 ? launch_attn<1, 1, 2, 128, true>(tq, tk, tv, to, p, st)
+                                        : launch_attn<1, 1, 1, 128, true>(tq, tk, tv, to, p, st);
+        if (d <= 128) return n_tiles > 2 ? launch_attn<2, 1, 2, 128, true>(tq, tk, tv, to, p, st)
+                                         : launch_attn<2, 1, 1, 128, true>(tq, tk, tv, to, p, st);
+        return launch_attn<3, 1, 1, 128, true>(tq, tk, tv, to, p, st);
+    }
     if (d <= 64) {
         if (nqt == 3) return launch_attn<1, 3, 4, 64>(tq, tk, tv, to, p, st);
         if (nqt == 2) return launch_attn<1, 2, 3>(tq, tk, tv, to, p, st);
@@ -655,4 +690,35 @@ extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, vo
         return n_tiles > 2 ? launch_attn<2, 1, 2>(tq, tk, tv, to, p, st) : launch_attn<2, 1, 1>(tq, tk, tv, to, p, st);
     }
     return launch_attn<3, 1, 1>(tq, tk, tv, to, p, st);
+}
+
+}  // namespace cgs
+
+extern "C" int cgs_attention_fwd(const void* q, const void* k, const void* v, void* out, int B,
+                                 int H, int Nq, int Nk, int d, long long q_stride_b,
+                                 long long q_stride_n, long long q_stride_h, long long k_stride_b,
+                                 long long k_stride_n, long long k_stride_h, long long v_stride_b,
+                                 long long v_stride_n, long long v_stride_h, long long o_stride_b,
+                                 long long o_stride_n, long long o_stride_h, float softmax_scale,
+                                 void* stream) {
+    return cgs::attention_entry(q, k, v, out, B, H, Nq, Nk, d, q_stride_b, q_stride_n, q_stride_h, k_stride_b,
+                                k_stride_n, k_stride_h, v_stride_b, v_stride_n, v_stride_h, o_stride_b, o_stride_n,
+                                o_stride_h, softmax_scale, nullptr, 0, 0, 0, stream);
+}
+
+extern "C" int cgs_attention_masked_fwd(const void* q, const void* k, const void* v, void* out, int B,
+                                        int H, int Nq, int Nk, int d, long long q_stride_b,
+                                        long long q_stride_n, long long q_stride_h, long long k_stride_b,
+                                        long long k_stride_n, long long k_stride_h, long long v_stride_b,
+                                        long long v_stride_n, long long v_stride_h, long long o_stride_b,
+                                        long long o_stride_n, long long o_stride_h, float softmax_scale,
+                                        const float* mask, long long mask_stride_b, long long mask_stride_h,
+                                        long long mask_stride_q, void* stream) {
+    if (mask == nullptr) {
+        cgs::set_last_error("attention_masked: mask must not be null (use cgs_attention_fwd)");
+        return cgs::kBadArgument;
+    }
+    return cgs::attention_entry(q, k, v, out, B, H, Nq, Nk, d, q_stride_b, q_stride_n, q_stride_h, k_stride_b,
+                                k_stride_n, k_stride_h, v_stride_b, v_stride_n, v_stride_h, o_stride_b, o_stride_n,
+                                o_stride_h, softmax_scale, mask, mask_stride_b, mask_stride_h, mask_stride_q, stream);
 }

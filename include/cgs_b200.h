@@ -55,6 +55,24 @@ int cgs_attention_fwd(const void* q, const void* k, const void* v, void* out,
                       float softmax_scale, void* stream);
 
 /*
+ * The same with an additive mask: softmax(q k^T * scale + mask) v. Replaces optimized_attention_masked(q, k, v, heads,
+ * mask) == attention_pytorch with attn_mask / attention_basic's mask branch (comfy/ldm/modules/attention.py:111-123,
+ * 337-349, 353-368). The UNet never passes a mask (attention.py:411-414, 520, 560); this entry exists so that the
+ * rebinding of optimized_attention_masked keeps the reference's other callers (nodes_sag.py:130, Stable Cascade) working.
+ *   mask: fp32, logically [B, H, Nq, Nk] with key stride 1 and element strides mask_stride_{b,h,q}; a stride of 0
+ *   broadcasts that dimension. Boolean "keep" masks are passed as 0 / -1e30 by the host (attention.py:113-117 fills with
+ *   -finfo.max, so a fully masked row is a uniform average there and here).
+ */
+int cgs_attention_masked_fwd(const void* q, const void* k, const void* v, void* out,
+                             int B, int H, int Nq, int Nk, int d,
+                             long long q_stride_b, long long q_stride_n, long long q_stride_h,
+                             long long k_stride_b, long long k_stride_n, long long k_stride_h,
+                             long long v_stride_b, long long v_stride_n, long long v_stride_h,
+                             long long o_stride_b, long long o_stride_n, long long o_stride_h,
+                             float softmax_scale, const float* mask, long long mask_stride_b,
+                             long long mask_stride_h, long long mask_stride_q, void* stream);
+
+/*
  * LayerNorm forward (L1). Replaces ops.LayerNorm.forward -> F.layer_norm
  * (comfy/ops.py:97-113) as norm1/norm2/norm3 (comfy/ldm/modules/attention.py:450-453).
  *   x, y [rows, C] bf16 contiguous; gamma, beta [C] bf16; C multiple of 8, <= 2560;

@@ -77,6 +77,22 @@ def gen_attention():
         assert (o_basic - o_torch).abs().max() < 1e-5
         out.update({f"{name}.q": q, f"{name}.k": k, f"{name}.v": v, f"{name}.out": o_torch,
                     f"{name}.heads": np.int64(h)})
+    # masked attention (attention.py:111-123, 345): additive float (causal-like, per-head, 2-D) and boolean keep-masks
+    g = torch.Generator().manual_seed(77)
+    masked = {
+        "mask_causal_4d": (2, 40, 40, 2, 64, torch.triu(torch.full((40, 40), float("-inf")), diagonal=1)[None, None]),
+        "mask_float_2d": (2, 48, 77, 2, 40, torch.randn((48, 77), generator=g) * 2.0),
+        "mask_float_per_head": (1, 33, 150, 3, 64, torch.randn((1, 3, 33, 150), generator=g)),
+        "mask_bool_keys": (2, 24, 77, 2, 64, (torch.rand((2, 1, 1, 77), generator=g) > 0.3)),
+    }
+    for name, (b, nq, nk, h, d, mask) in masked.items():
+        q, k, v = randn((b, nq, h * d), 4), randn((b, nk, h * d), 5), randn((b, nk, h * d), 6)
+        o_torch = ra.attention_pytorch(q, k, v, h, mask=mask)
+        if mask.dtype != torch.bool:        # attention_basic takes 2-D / 3-D / [bs, x, Nq, Nk] float masks
+            o_basic = ra.attention_basic(q, k, v, h, mask=mask)
+            assert (o_basic - o_torch).abs().max() < 1e-5, name
+        out.update({f"{name}.q": q, f"{name}.k": k, f"{name}.v": v, f"{name}.out": o_torch, f"{name}.mask": mask,
+                    f"{name}.heads": np.int64(h)})
     save("attention", **out)
 
 
@@ -251,6 +267,8 @@ def gen_e2e(family, seed, batch, hw, steps, sampler, scheduler, pos_len, neg_len
 def main():
     torch.manual_seed(0)
     gen_attention()
+    if "--only-attention" in sys.argv:
+        return
     gen_blocks()
     gen_schedules()
     gen_sampler_kat()

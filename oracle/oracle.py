@@ -26,15 +26,27 @@ Tensor = torch.Tensor
 # ----------------------------------------------------------------------------------------------
 # attention / transformer block   (comfy/ldm/modules/attention.py)
 # ----------------------------------------------------------------------------------------------
-def attention(q: Tensor, k: Tensor, v: Tensor, heads: int) -> Tensor:
-    """attention_basic / attention_pytorch, mask None (attention.py:88-140, 337-349):
-    q [B,Nq,H*d], k/v [B,Nk,H*d] -> softmax(q k^T / sqrt(d)) v, heads interleaved in the last dim."""
+def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, mask: Optional[Tensor] = None) -> Tensor:
+    """attention_basic / attention_pytorch (attention.py:88-140, 337-349):
+    q [B,Nq,H*d], k/v [B,Nk,H*d] -> softmax(q k^T / sqrt(d) (+ mask)) v, heads interleaved in the last dim.
+    mask (attention.py:111-123): bool keep-mask -> masked_fill(~mask, -finfo.max); float -> added to the scaled scores;
+    2-D [Nq,Nk], 3-D [bs,Nq,Nk] or broadcastable to [B,H,Nq,Nk]."""
     b, nq, inner = q.shape
     d = inner // heads
     qh = q.float().reshape(b, nq, heads, d).permute(0, 2, 1, 3)
     kh = k.float().reshape(b, -1, heads, d).permute(0, 2, 1, 3)
     vh = v.float().reshape(b, -1, heads, d).permute(0, 2, 1, 3)
     sim = torch.matmul(qh, kh.transpose(-1, -2)) * (d ** -0.5)
+    if mask is not None:
+        m = mask
+        if m.dim() == 2:
+            m = m[None, None]
+        elif m.dim() == 3:
+            m = m[:, None]
+        if m.dtype == torch.bool:
+            sim = sim.masked_fill(~m.expand_as(sim), -torch.finfo(sim.dtype).max)
+        else:
+            sim = sim + m.float()
     out = torch.matmul(sim.softmax(dim=-1), vh)
     return out.permute(0, 2, 1, 3).reshape(b, nq, inner)
 

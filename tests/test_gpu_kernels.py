@@ -40,6 +40,38 @@ def test_attention_golden(name):
     assert (out - ref).abs().max() < ATTN_TOL / 2                   # vs the oracle on the same bf16 inputs
 
 
+@pytest.mark.parametrize("name", ["mask_causal_4d", "mask_float_2d", "mask_float_per_head", "mask_bool_keys"])
+def test_masked_attention_golden(name):
+    """optimized_attention_masked: additive float and boolean keep-masks in the reference's shapes."""
+    g = load_golden("attention")
+    q, k, v, h, mask = g[f"{name}.q"], g[f"{name}.k"], g[f"{name}.v"], int(g[f"{name}.heads"]), g[f"{name}.mask"]
+    out = N().attention(bf(q), bf(k), bf(v), h, mask.cuda()).float().cpu()
+    assert (out - g[f"{name}.out"]).abs().max() < ATTN_TOL
+    ref = O.attention(bf(q).float().cpu(), bf(k).float().cpu(), bf(v).float().cpu(), h, mask)
+    assert (out - ref).abs().max() < ATTN_TOL / 2
+
+
+def test_masked_attention_large_and_fully_masked_rows():
+    """Several key tiles with a mask (the two-stage variant), a broadcast key dimension, and rows whose keys are all
+    masked by a boolean mask: a uniform average, as attention.py:113-117 gives (-finfo.max fill)."""
+    n = N()
+    B, H, Nq, Nk, d = 2, 4, 300, 700, 64
+    q, k, v = bf(randn((B, Nq, H * d), 1)), bf(randn((B, Nk, H * d), 2)), bf(randn((B, Nk, H * d), 3))
+    mask = randn((B, 1, Nq, Nk), 4).cuda() * 3.0
+    ref = O.attention(q.float().cpu(), k.float().cpu(), v.float().cpu(), H, mask.cpu())
+    assert (n.attention(q, k, v, H, mask).float().cpu() - ref).abs().max() < ATTN_TOL
+    per_query = randn((Nq, 1), 5).cuda()                       # key dimension broadcast: no effect on the softmax
+    base = n.attention(q, k, v, H)
+    assert (n.attention(q, k, v, H, per_query).float() - base.float()).abs().max() < 2e-2
+    keep = torch.ones((B, 1, Nq, Nk), dtype=torch.bool, device="cuda")
+    keep[0, 0, 5] = False                                         # one fully masked row
+    keep[:, :, :, 350:] = False
+    keep[0, 0, 5] = False
+    out = n.attention(q, k, v, H, keep).float().cpu()
+    ref = O.attention(q.float().cpu(), k.float().cpu(), v.float().cpu(), H, keep.cpu())
+    assert torch.isfinite(out).all() and (out - ref).abs().max() < ATTN_TOL
+
+
 ATTN_SHAPES = [
     # B, H, Nq, Nk, d          -- the geometries of SURVEY.md section 8 (scaled-down batch)
     (2, 10, 4096, 4096, 64), (1, 20, 1024, 1024, 64), (2, 10, 4096, 77, 64), (2, 20, 1024, 154, 64),

@@ -18,6 +18,14 @@ def test_attention_matches_reference():
         assert (out - g[f"{name}.out"]).abs().max() < TOL, name
 
 
+def test_masked_attention_matches_reference():
+    """attention.py:111-123 / SDPA attn_mask: additive float masks (4-D causal, 2-D, per-head) and a boolean key mask."""
+    g = load_golden("attention")
+    for name in ("mask_causal_4d", "mask_float_2d", "mask_float_per_head", "mask_bool_keys"):
+        out = O.attention(g[f"{name}.q"], g[f"{name}.k"], g[f"{name}.v"], int(g[f"{name}.heads"]), g[f"{name}.mask"])
+        assert (out - g[f"{name}.out"]).abs().max() < TOL, name
+
+
 def _weights(prefix_shapes, seed):
     return uc.seeded_state_dict(prefix_shapes, seed)
 
