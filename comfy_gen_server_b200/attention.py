@@ -158,12 +158,19 @@ class CrossAttention(nn.Module):
         out = optimized_attention(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], self.heads)
         return self.to_out(out)
 
+    def _kv_key(self, context):
+        return (context.data_ptr(), _ver(context), tuple(context.shape), self.to_k.weight.data_ptr(),
+                _ver(self.to_k.weight), self.to_v.weight.data_ptr(), _ver(self.to_v.weight))
+
+    def set_kv_cache(self, context, k, v):
+        """Install K/V computed by the caller for `context` (the step-graph code keeps them at fixed addresses)."""
+        self._kv_cache = (self._kv_key(context), k, v, context)
+
     def forward_cross_cached(self, x, context):
         """Cross-attention: K/V depend only on the context; reuse them while it is unchanged."""
         if not self._plain_weights():
             return self.forward(x, context)
-        key = (context.data_ptr(), _ver(context), tuple(context.shape), self.to_k.weight.data_ptr(),
-               _ver(self.to_k.weight), self.to_v.weight.data_ptr(), _ver(self.to_v.weight))
+        key = self._kv_key(context)
         if self._kv_cache is None or self._kv_cache[0] != key:
             self._kv_cache = (key, self.to_k(context), self.to_v(context), context)  # keeps context alive
         _, k, v, _ = self._kv_cache

@@ -506,6 +506,8 @@ class CFGGuider:
         tables = st["tables"]
         sigma_f = float(sigma_hat)
         st["calls"] += 1
+        if st["graph"] is None and st["calls"] == 1 and st["graph_opt"] not in (False, None):
+            st["graph"] = self._reuse_step_graph(st, x, model_options)      # captured by an earlier sample() call?
         if st["graph"] is None and st["calls"] >= 3:
             st["graph"] = self._maybe_capture_step(st, x, model_options)
         if st["graph"]:
@@ -567,9 +569,12 @@ class CFGGuider:
         g = {
             "P": torch.zeros(n_par, device=x.device, dtype=torch.float32),
             "X": torch.empty_like(x), "XN": torch.empty_like(x), "DEN": torch.empty_like(x),
-            "OLD": torch.zeros_like(x), "stage": torch.zeros(64, n_par, dtype=torch.float32).pin_memory(),
-            "last_den": None,
+            "OLD": torch.zeros_like(x), "last_den": None,
+            # the conditioning lives in buffers of the graph's own, so that a later sample() call with other prompts
+            # can reuse the graph: copy the new context in, recompute the cross-attention K/V in place, replay
+            "CTX": st["context"].clone(), "Y": None if st["y"] is None else st["y"].clone(),
         }
+        g["kv"] = self._prime_kv_caches(g["CTX"], None)
         sigma_vec, t_vec, step = g["P"][:b], g["P"][b:b + b * copies], g["P"][b + b * copies:]
         topt = dict(model_options.get("transformer_options", {}))
         topt["cond_or_uncond"] = list(st["cond_or_uncond"])
@@ -578,7 +583,7 @@ class CFGGuider:
 
         def body():
             xc = _native.unet_input(g["X"], sigma_vec, copies, sigma_data)
-            out = m.unet_raw(xc, t_vec, st["context"], st["y"], topt)
+            out = m.unet_raw(xc, t_vec, g["CTX"], g["Y"], topt)
             if not out.is_contiguous():
                 out = out.contiguous()
             out_u, out_c = self._split_outputs(out, b, st)
@@ -595,21 +600,80 @@ class CFGGuider:
         for k, v in g["counts"].items():
             _native.LAUNCHES[k] -= v
         g["graph"] = graph
+        cache = m.__dict__.setdefault("_step_graphs", collections.OrderedDict())
+        cache[self._graph_key(st, x, model_options)] = g
+        while len(cache) > 2:                              # a graph pins its activation pool: keep the two latest
+            cache.popitem(last=False)
+        return g
+
+    # -- graphs that outlive a sample() call ----------------------------------------------------------
+    def _graph_key(self, st, x, model_options):
+        """Everything that is baked into a captured step: shapes, scalars that are kernel arguments, and the
+        identity of the weights (a LoRA patch or a reload replaces or rewrites parameter tensors)."""
+        m = self.inner_model
+        params = list(m.diffusion_model.parameters())
+        weights = tuple((p.data_ptr(), p._version) for p in params[::37])
+        topt = model_options.get("transformer_options", {})
+        return (tuple(x.shape), str(x.device), st["copies"], tuple(st["cond_or_uncond"]), float(self.cfg),
+                m.model_sampling.pred_type, float(m.model_sampling.sigma_data), tuple(st["context"].shape),
+                None if st["y"] is None else tuple(st["y"].shape), tuple(sorted(map(str, topt.keys()))),
+                len(params), weights)
+
+    def _cross_attention_modules(self):
+        from .attention import CrossAttention
+        return [mod for mod in self.inner_model.diffusion_model.modules() if isinstance(mod, CrossAttention)]
+
+    def _prime_kv_caches(self, ctx, kv):
+        """Cross-attention K/V of `ctx` for every layer that caches them. First time (kv None): fresh tensors, handed
+        to the layers' caches, so that the capture bakes their addresses. Later: recomputed into the same tensors."""
+        out = []
+        if kv is None:
+            for mod in self._cross_attention_modules():
+                if mod._kv_cache is None:
+                    continue                                   # a layer that did not take the cached path
+                k, v = mod.to_k(ctx), mod.to_v(ctx)
+                mod.set_kv_cache(ctx, k, v)
+                out.append((mod, k, v))
+            return out
+        for mod, k, v in kv:
+            k.copy_(mod.to_k(ctx))
+            v.copy_(mod.to_v(ctx))
+            mod.set_kv_cache(ctx, k, v)
+        return kv
+
+    def _reuse_step_graph(self, st, x, model_options):
+        if type(self) is not CFGGuider or _native._timed_family is not None:
+            return None
+        cache = self.inner_model.__dict__.get("_step_graphs")
+        if not cache:
+            return None
+        key = self._graph_key(st, x, model_options)
+        g = cache.get(key)
+        if g is None:
+            return None
+        cache.move_to_end(key)
+        g["CTX"].copy_(st["context"])
+        if g["Y"] is not None:
+            g["Y"].copy_(st["y"])
+        self._prime_kv_caches(g["CTX"], g["kv"])
+        g["last_den"] = None
         return g
 
     def _graph_step(self, st, x, i, sigma_f, sampler, c0, c1, c2, c3, old_denoised):
         g = st["graph"]
         b, copies = x.shape[0], st["copies"]
-        if i >= g["stage"].shape[0]:
-            grown = torch.zeros(2 * (i + 1), g["stage"].shape[1], dtype=torch.float32).pin_memory()
-            grown[:g["stage"].shape[0]] = g["stage"]
-            g["stage"] = grown
+        if st.get("stage") is None:                       # pinned rows of this sample() call (not the graph's: the host
+            st["stage"] = torch.zeros(64, g["P"].numel(), dtype=torch.float32).pin_memory()   # runs steps ahead)
+        if i >= st["stage"].shape[0]:
+            grown = torch.zeros(2 * (i + 1), st["stage"].shape[1], dtype=torch.float32).pin_memory()
+            grown[:st["stage"].shape[0]] = st["stage"]
+            st["stage"] = grown
         tables = st["tables"]
         if tables is not None and i < len(tables[2]) and float(tables[2][i]) == sigma_f:
             t = float(tables[3][i])
         else:
             t = float(self.inner_model.model_sampling.timestep(torch.tensor([sigma_f]))[0])
-        row = g["stage"][i]                              # one pinned row per step: never rewritten while in flight
+        row = st["stage"][i]                             # one pinned row per step: never rewritten while in flight
         row[:b] = sigma_f
         row[b:b + b * copies] = t
         row[b + b * copies:b + b * copies + 5] = torch.tensor([float(sampler), c0, c1, c2, c3])

@@ -220,6 +220,34 @@ def test_cuda_graph_step_replay_equals_launch_by_launch(golden, family, sampler,
     assert launches[1] >= launches[0] - 2 and launches[0] > 0        # replays count the kernels they launch
 
 
+def test_cuda_graph_is_reused_across_sample_calls_with_new_prompts():
+    """A captured step outlives its sample() call: the next call with the same shapes copies its prompts into the
+    graph's conditioning buffers, recomputes the cross-attention K/V in place and replays from the first step."""
+    from comfy_gen_server_b200 import sample as S
+    g = load_golden("e2e_tiny_sdxl_dpmpp2m")
+    seed = int(g["seed"])
+    patcher = _patcher("tiny_sdxl", seed)
+    latent = torch.zeros(2, 4, 16, 16)
+    noise = S.prepare_noise(latent, seed)
+    prompts = []
+    for k in range(2):
+        e = lambda shape, s_: randn(shape, 900 + 10 * k + s_)
+        prompts.append(([[e((1, 77, g["positive"].shape[-1]), 1), {"pooled_output": e((1, 1280), 2)}]],
+                        [[e((1, 77, g["positive"].shape[-1]), 3), {"pooled_output": e((1, 1280), 4)}]]))
+    run = lambda p, pn: S.sample(p, noise, 6, 7.0, "dpmpp_2m", "karras", pn[0], pn[1], latent, seed=seed)
+    with torch.inference_mode():
+        plain = patcher.clone()
+        plain.model_options["cuda_graph"] = False
+        want = [run(plain, pn) for pn in prompts]
+        graphed = patcher.clone()
+        graphed.model_options["cuda_graph"] = True
+        got = [run(graphed, prompts[0]), run(graphed, prompts[1]), run(graphed, prompts[0])]
+    cache = patcher.model.__dict__.get("_step_graphs")
+    assert cache is not None and len(cache) == 1                 # one capture served all three calls
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1]) and torch.equal(got[2], want[0])
+    assert not torch.equal(want[0], want[1])
+
+
 def test_channels_last_pipeline_matches_nchw_pipeline():
     """the NHWC end-to-end UNet (channels_last GroupNorm kernels, cuDNN NHWC convs, free token views)
     gives the same latents as the NCHW pipeline."""
