@@ -30,6 +30,8 @@ _SIGNATURES = {
     "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_fwd": [_c_void_p] * 6 + [_c_ll] + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_noalloc_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
+    "cgs_cat_channels_nhwc_fwd": [_c_void_p] * 3 + [_c_ll, _c_int, _c_int, _c_void_p],
+    "cgs_upsample_nearest2x_nhwc_fwd": [_c_void_p] * 2 + [_c_int] * 4 + [_c_void_p],
     "cgs_add_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_ll, _c_void_p],
     "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
@@ -338,6 +340,39 @@ def residual_add(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] 
     if bias is not None:
         out = out + bias.to(out.dtype).view(1, -1, *([1] * (out.dim() - 2)))
     return out
+
+
+def _is_nhwc_bf16(t: torch.Tensor) -> bool:
+    return (t.is_cuda and t.dtype == torch.bfloat16 and t.dim() == 4 and not t.is_contiguous()
+            and t.is_contiguous(memory_format=torch.channels_last))
+
+
+def cat_channels(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """torch.cat([a, b], dim=1) for channels-last bf16 images (the UNet's skip concatenation); any other layout is
+    torch.cat, the reference's own call."""
+    if (_is_nhwc_bf16(a) and _is_nhwc_bf16(b) and a.shape[0] == b.shape[0] and a.shape[2:] == b.shape[2:]
+            and a.shape[1] % 8 == 0 and b.shape[1] % 8 == 0):
+        n, ca, h, w = a.shape
+        cb = b.shape[1]
+        out = torch.empty((n, ca + cb, h, w), dtype=a.dtype, device=a.device, memory_format=torch.channels_last)
+        with _Launch("cat_channels", a, 4.0 * out.numel()):
+            rc = load_library().cgs_cat_channels_nhwc_fwd(a.data_ptr(), b.data_ptr(), out.data_ptr(), n * h * w, ca, cb,
+                                                          _stream(a))
+        _check(rc, "cgs_cat_channels_nhwc_fwd")
+        return out
+    return torch.cat([a, b], dim=1)
+
+
+def upsample_nearest2x(x: torch.Tensor) -> torch.Tensor:
+    """F.interpolate(x, scale 2, mode='nearest') for channels-last bf16 images; anything else is the torch call."""
+    if _is_nhwc_bf16(x) and x.shape[1] % 8 == 0:
+        n, c, h, w = x.shape
+        out = torch.empty((n, c, 2 * h, 2 * w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        with _Launch("upsample2x", x, 2.0 * 5 * x.numel()):
+            rc = load_library().cgs_upsample_nearest2x_nhwc_fwd(x.data_ptr(), out.data_ptr(), n, h, w, c, _stream(x))
+        _check(rc, "cgs_upsample_nearest2x_nhwc_fwd")
+        return out
+    return torch.nn.functional.interpolate(x, scale_factor=2, mode="nearest")
 
 
 def transpose_add(x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:

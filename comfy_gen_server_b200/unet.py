@@ -65,7 +65,10 @@ class Upsample(nn.Module):
         shape = [x.shape[2] * 2, x.shape[3] * 2]
         if output_shape is not None:
             shape = [output_shape[2], output_shape[3]]
-        x = F.interpolate(x, size=shape, mode="nearest")
+        if shape == [x.shape[2] * 2, x.shape[3] * 2] and x.is_cuda:
+            x = _native.upsample_nearest2x(x)
+        else:
+            x = F.interpolate(x, size=shape, mode="nearest")
         if self.use_conv:
             x = self.conv(x)
         return x
@@ -302,7 +305,7 @@ class UNetModel(nn.Module):
             hsp = apply_control(hsp, control, 'output')
             for p in transformer_patches.get("output_block_patch", []):
                 h, hsp = p(h, hsp, transformer_options)
-            h = torch.cat([h, hsp], dim=1)
+            h = _native.cat_channels(h, hsp) if h.is_cuda else torch.cat([h, hsp], dim=1)
             del hsp
             output_shape = hs[-1].shape if len(hs) > 0 else None
             h = forward_timestep_embed(module, h, emb, context, transformer_options, output_shape)

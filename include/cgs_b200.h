@@ -153,6 +153,19 @@ int cgs_add_fwd(const void* a, const void* b, const void* bias, void* out, long 
                 void* stream);
 
 /*
+ * Channel concatenation of two channels-last images: out[p, 0:ca] = a[p, :], out[p, ca:ca+cb] = b[p, :] for each of
+ * `pixels` = N*H*W pixels; bf16, ca and cb multiples of 8. Replaces `th.cat([h, hs.pop()], dim=1)`
+ * (comfy/ldm/modules/diffusionmodules/openaimodel.py:869) in the channels-last pipeline.
+ */
+int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, void* out, long long pixels, int ca, int cb, void* stream);
+
+/*
+ * Nearest-neighbour 2x up-sampling of a channels-last image: x [N, H, W, C] -> out [N, 2H, 2W, C], bf16, C % 8 == 0.
+ * Replaces F.interpolate(x, size=(2H, 2W), mode="nearest") in Upsample.forward (openaimodel.py:86-93).
+ */
+int cgs_upsample_nearest2x_nhwc_fwd(const void* x, void* out, int N, int H, int W, int C, void* stream);
+
+/*
  * GEGLU projection (G1): y[m, n] = (x W^T + b)[m, n] * gelu_erf((x W^T + b)[m, N + n]).
  * Replaces GEGLU.forward: Linear -> chunk(2) -> F.gelu -> mul
  * (comfy/ldm/modules/attention.py:56-63).

@@ -258,6 +258,21 @@ def test_residual_add_layouts():
     assert torch.equal(n.residual_add(a2, b2, bf(randn((12,), 7))), want2)
 
 
+def test_cat_channels_and_upsample_nhwc():
+    n = N()
+    cl = lambda t: t.contiguous(memory_format=torch.channels_last)
+    a, b = bf(randn((2, 320, 12, 20), 1)), bf(randn((2, 640, 12, 20), 2))
+    out = n.cat_channels(cl(a), cl(b))
+    assert out.is_contiguous(memory_format=torch.channels_last) and torch.equal(out, torch.cat([a, b], dim=1))
+    assert torch.equal(n.cat_channels(a, b), torch.cat([a, b], dim=1))              # NCHW: torch path
+    up = n.upsample_nearest2x(cl(a))
+    assert up.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(up, torch.nn.functional.interpolate(a, scale_factor=2, mode="nearest"))
+    assert torch.equal(n.upsample_nearest2x(a), torch.nn.functional.interpolate(a, scale_factor=2, mode="nearest"))
+    big = bf(randn((1, 8, 3, 5), 3))                                                  # odd spatial sizes
+    assert torch.equal(n.upsample_nearest2x(cl(big)), torch.nn.functional.interpolate(big, scale_factor=2, mode="nearest"))
+
+
 def test_resblock_bias_folding_matches_plain_path():
     """ResBlock with conv biases folded into GroupNorm's add_nc / the residual add vs the same block run op by op."""
     from comfy_gen_server_b200 import unet
