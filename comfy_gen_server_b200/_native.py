@@ -30,7 +30,7 @@ _SIGNATURES = {
     "cgs_groupnorm_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_fwd": [_c_void_p] * 6 + [_c_ll] + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
     "cgs_groupnorm_nhwc_noalloc_fwd": [_c_void_p] * 5 + [_c_int] * 4 + [_c_float, _c_int, _c_void_p],
-    "cgs_cat_channels_nhwc_fwd": [_c_void_p] * 3 + [_c_ll, _c_int, _c_int, _c_void_p],
+    "cgs_cat_channels_nhwc_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_void_p],
     "cgs_upsample_nearest2x_nhwc_fwd": [_c_void_p] * 2 + [_c_int] * 4 + [_c_void_p],
     "cgs_add_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_ll, _c_void_p],
     "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
@@ -347,17 +347,22 @@ def _is_nhwc_bf16(t: torch.Tensor) -> bool:
             and t.is_contiguous(memory_format=torch.channels_last))
 
 
-def cat_channels(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
-    """torch.cat([a, b], dim=1) for channels-last bf16 images (the UNet's skip concatenation); any other layout is
-    torch.cat, the reference's own call."""
+def cat_channels(a: torch.Tensor, b: torch.Tensor, bias_a: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """torch.cat([a (+ bias_a[None, :, None, None]), b], dim=1) for channels-last bf16 images (the UNet's skip
+    concatenation); any other layout is torch.cat, the reference's own call."""
+    if bias_a is not None and not (bias_a.dtype == torch.bfloat16 and bias_a.is_cuda and bias_a.is_contiguous()
+                                   and _is_nhwc_bf16(a) and _is_nhwc_bf16(b)):
+        a = a + bias_a.to(a.dtype).view(1, -1, 1, 1)
+        bias_a = None
     if (_is_nhwc_bf16(a) and _is_nhwc_bf16(b) and a.shape[0] == b.shape[0] and a.shape[2:] == b.shape[2:]
             and a.shape[1] % 8 == 0 and b.shape[1] % 8 == 0):
         n, ca, h, w = a.shape
         cb = b.shape[1]
         out = torch.empty((n, ca + cb, h, w), dtype=a.dtype, device=a.device, memory_format=torch.channels_last)
         with _Launch("cat_channels", a, 4.0 * out.numel()):
-            rc = load_library().cgs_cat_channels_nhwc_fwd(a.data_ptr(), b.data_ptr(), out.data_ptr(), n * h * w, ca, cb,
-                                                          _stream(a))
+            rc = load_library().cgs_cat_channels_nhwc_fwd(a.data_ptr(), b.data_ptr(),
+                                                          None if bias_a is None else bias_a.data_ptr(),
+                                                          out.data_ptr(), n * h * w, ca, cb, _stream(a))
         _check(rc, "cgs_cat_channels_nhwc_fwd")
         return out
     return torch.cat([a, b], dim=1)

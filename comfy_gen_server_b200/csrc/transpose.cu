@@ -109,16 +109,29 @@ add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const __nv_
 
 // Channel concatenation of two channels-last images (the UNet's skip connections, `th.cat([h, hs.pop()], dim=1)`,
 // openaimodel.py:869): out[p, 0:Ca] = a[p, :], out[p, Ca:Ca+Cb] = b[p, :] for every pixel p, 16 bytes per thread.
-// ATen's CatArrayBatchedCopy moved these at 1.3 TB/s.
+// ATen's CatArrayBatchedCopy moved these at 1.3 TB/s. bias_a (optional, [Ca]) is added to the `a` part: the bias of
+// the Upsample convolution that produced `a`, which ATen would add in a separate full pass over the 2x-larger image.
 __global__ void __launch_bounds__(256)
-cat_channels_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out,
-                    long long pixels, int ca8, int cb8) {
+cat_channels_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const __nv_bfloat16* __restrict__ bias_a,
+                    uint4* __restrict__ out, long long pixels, int ca8, int cb8) {
     const int c8 = ca8 + cb8;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= pixels * c8) return;
     const long long pix = i / c8;
     const int c = (int)(i - pix * c8);
-    out[i] = c < ca8 ? a[pix * ca8 + c] : b[pix * cb8 + (c - ca8)];
+    if (c >= ca8) {
+        out[i] = b[pix * cb8 + (c - ca8)];
+        return;
+    }
+    uint4 v = a[pix * ca8 + c];
+    if (bias_a != nullptr) {
+        const uint4 bb = *reinterpret_cast<const uint4*>(bias_a + c * 8);
+        __nv_bfloat162* vv = reinterpret_cast<__nv_bfloat162*>(&v);
+        const __nv_bfloat162* bv = reinterpret_cast<const __nv_bfloat162*>(&bb);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) vv[k] = __hadd2_rn(vv[k], bv[k]);
+    }
+    out[i] = v;
 }
 
 // Nearest-neighbour 2x up-sampling of a channels-last image (Upsample.forward, openaimodel.py:86-95, for the exact
@@ -145,8 +158,8 @@ upsample2x_nhwc_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, lon
 
 }  // namespace cgs
 
-extern "C" int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, void* out, long long pixels, int ca, int cb,
-                                         void* stream) {
+extern "C" int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, const void* bias_a, void* out, long long pixels,
+                                         int ca, int cb, void* stream) {
     using namespace cgs;
     if (pixels < 0 || ca <= 0 || cb <= 0) {
         set_last_error("cat_channels: bad sizes pixels=%lld ca=%d cb=%d", pixels, ca, cb);
@@ -154,7 +167,7 @@ extern "C" int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, void* out
     }
     if (pixels == 0) return kOk;
     if (ca % 8 != 0 || cb % 8 != 0 || ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
-                                         reinterpret_cast<uintptr_t>(out)) & 0xF)) {
+                                         reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(bias_a)) & 0xF)) {
         set_last_error("cat_channels: channel counts must be multiples of 8 and pointers 16-byte aligned");
         return kUnsupportedShape;
     }
@@ -165,7 +178,8 @@ extern "C" int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, void* out
         return kUnsupportedShape;
     }
     cat_channels_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), pixels, ca / 8, cb / 8);
+        static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<const __nv_bfloat16*>(bias_a),
+        static_cast<uint4*>(out), pixels, ca / 8, cb / 8);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }

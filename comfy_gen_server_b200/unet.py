@@ -61,7 +61,9 @@ class Upsample(nn.Module):
             self.conv = operations.conv_nd(dims, self.channels, self.out_channels, 3, padding=padding, dtype=dtype,
                                            device=device)
 
-    def forward(self, x, output_shape=None):
+    def forward(self, x, output_shape=None, bias_out=None):
+        """bias_out (a list): when given and the conv can run bias-free, its bias is appended there instead of being
+        added here -- the caller folds it into the skip concatenation that consumes this output."""
         shape = [x.shape[2] * 2, x.shape[3] * 2]
         if output_shape is not None:
             shape = [output_shape[2], output_shape[3]]
@@ -70,7 +72,12 @@ class Upsample(nn.Module):
         else:
             x = F.interpolate(x, size=shape, mode="nearest")
         if self.use_conv:
-            x = self.conv(x)
+            conv = self.conv
+            if (bias_out is not None and x.is_cuda and x.dtype == torch.bfloat16 and hasattr(conv, "forward_nobias")
+                    and not conv.comfy_cast_weights and conv.bias is not None and conv.bias.dtype == torch.bfloat16):
+                bias_out.append(conv.bias)
+                return conv.forward_nobias(x)
+            x = conv(x)
         return x
 
 
@@ -135,8 +142,8 @@ class ResBlock(TimestepBlock):
         return _native.residual_add(self.skip_connection(x), h)
 
 
-def forward_timestep_embed(ts, x, emb, context=None, transformer_options={}, output_shape=None):
-    """openaimodel.py:33-51."""
+def forward_timestep_embed(ts, x, emb, context=None, transformer_options={}, output_shape=None, up_bias=None):
+    """openaimodel.py:33-51. up_bias: see Upsample.forward."""
     for layer in ts:
         if isinstance(layer, TimestepBlock):
             x = layer(x, emb)
@@ -145,7 +152,7 @@ def forward_timestep_embed(ts, x, emb, context=None, transformer_options={}, out
             if "transformer_index" in transformer_options:
                 transformer_options["transformer_index"] += 1
         elif isinstance(layer, Upsample):
-            x = layer(x, output_shape=output_shape)
+            x = layer(x, output_shape=output_shape, bias_out=up_bias)
         else:
             x = layer(x)
     return x
@@ -299,15 +306,21 @@ class UNetModel(nn.Module):
             h = forward_timestep_embed(self.middle_block, h, emb, context, transformer_options)
         h = apply_control(h, control, 'middle')
 
+        # an Upsample conv's bias is added by the next skip concatenation (nothing reads h in between unless a control
+        # net or an output_block_patch is installed)
+        defer = [] if control is None and not transformer_patches.get("output_block_patch") else None
         for id, module in enumerate(self.output_blocks):
             transformer_options["block"] = ("output", id)
             hsp = hs.pop()
             hsp = apply_control(hsp, control, 'output')
             for p in transformer_patches.get("output_block_patch", []):
                 h, hsp = p(h, hsp, transformer_options)
-            h = _native.cat_channels(h, hsp) if h.is_cuda else torch.cat([h, hsp], dim=1)
+            pending = defer.pop() if defer else None
+            h = _native.cat_channels(h, hsp, pending) if h.is_cuda else torch.cat([h, hsp], dim=1)
             del hsp
             output_shape = hs[-1].shape if len(hs) > 0 else None
-            h = forward_timestep_embed(module, h, emb, context, transformer_options, output_shape)
+            last = id == len(self.output_blocks) - 1
+            h = forward_timestep_embed(module, h, emb, context, transformer_options, output_shape,
+                                       None if last else defer)
         h = h.type(x.dtype)
         return self.out[2](_norm_silu(self.out[0], h))

@@ -155,9 +155,11 @@ int cgs_add_fwd(const void* a, const void* b, const void* bias, void* out, long 
 /*
  * Channel concatenation of two channels-last images: out[p, 0:ca] = a[p, :], out[p, ca:ca+cb] = b[p, :] for each of
  * `pixels` = N*H*W pixels; bf16, ca and cb multiples of 8. Replaces `th.cat([h, hs.pop()], dim=1)`
- * (comfy/ldm/modules/diffusionmodules/openaimodel.py:869) in the channels-last pipeline.
+ * (comfy/ldm/modules/diffusionmodules/openaimodel.py:869) in the channels-last pipeline. bias_a (NULL or [ca] bf16) is
+ * added to the `a` part: the bias of the Upsample convolution (openaimodel.py:94-95) that produced it.
  */
-int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, void* out, long long pixels, int ca, int cb, void* stream);
+int cgs_cat_channels_nhwc_fwd(const void* a, const void* b, const void* bias_a, void* out, long long pixels,
+                              int ca, int cb, void* stream);
 
 /*
  * Nearest-neighbour 2x up-sampling of a channels-last image: x [N, H, W, C] -> out [N, 2H, 2W, C], bf16, C % 8 == 0.

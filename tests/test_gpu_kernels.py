@@ -265,6 +265,10 @@ def test_cat_channels_and_upsample_nhwc():
     out = n.cat_channels(cl(a), cl(b))
     assert out.is_contiguous(memory_format=torch.channels_last) and torch.equal(out, torch.cat([a, b], dim=1))
     assert torch.equal(n.cat_channels(a, b), torch.cat([a, b], dim=1))              # NCHW: torch path
+    bias = bf(randn((320,), 9))
+    want = torch.cat([a + bias.view(1, -1, 1, 1), b], dim=1)
+    assert torch.equal(n.cat_channels(cl(a), cl(b), bias), want)
+    assert torch.equal(n.cat_channels(a, b, bias), want)
     up = n.upsample_nearest2x(cl(a))
     assert up.is_contiguous(memory_format=torch.channels_last)
     assert torch.equal(up, torch.nn.functional.interpolate(a, scale_factor=2, mode="nearest"))
