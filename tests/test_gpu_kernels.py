@@ -423,3 +423,55 @@ def test_tail_errors():
         n.cfg_denoise(x, None, x, torch.ones(1).cuda(), 1.0, 0)
     with pytest.raises(RuntimeError):
         n.sampler_step_euler(randn((1, 4, 4, 4), 1), randn((1, 4, 4, 4), 1), 1.0, 1.0)      # CPU tensors
+
+
+# ------------------------------------------------------------------------------------------ guard bands
+def test_kernels_write_only_their_output_window():
+    """Outputs placed inside larger sentinel-filled buffers: ragged rows, partial column tiles and head dims that are
+    not multiples of the 64-wide TMA box must not be written outside the logical output (TMA store clipping, row /
+    column predicates). Called through the C-ABI with explicit strides."""
+    n = N()
+    lib = n.load_library()
+    stream = torch.cuda.current_stream().cuda_stream
+    SENT = 777.0
+
+    # attention: B 2, H 3, Nq 200 (one full + one ragged query tile), Nk 77, d 40; output rows padded, columns padded
+    B, H, Nq, Nk, d = 2, 3, 200, 77, 40
+    q, k, v = bf(randn((B, Nq, H * d), 1)), bf(randn((B, Nk, H * d), 2)), bf(randn((B, Nk, H * d), 3))
+    row, rows = H * d + 64, Nq + 56
+    buf = torch.full((B, rows, row), SENT, dtype=torch.bfloat16, device="cuda")
+    rc = lib.cgs_attention_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), buf.data_ptr(), B, H, Nq, Nk, d,
+                               q.stride(0), q.stride(1), d, k.stride(0), k.stride(1), d, v.stride(0), v.stride(1), d,
+                               buf.stride(0), buf.stride(1), d, float(d) ** -0.5, stream)
+    assert rc == 0, lib.cgs_last_error()
+    want = n.attention(q, k, v, H)
+    assert torch.equal(buf[:, :Nq, :H * d], want)
+    assert (buf[:, Nq:, :] == SENT).all() and (buf[:, :, H * d:] == SENT).all()
+    # the same for a long key sequence (multi-tile variant, plain stores)
+    Nq2, Nk2 = 300, 1500
+    q2, k2, v2 = bf(randn((1, Nq2, 64), 4)), bf(randn((1, Nk2, 64), 5)), bf(randn((1, Nk2, 64), 6))
+    buf2 = torch.full((1, Nq2 + 100, 64 + 64), SENT, dtype=torch.bfloat16, device="cuda")
+    rc = lib.cgs_attention_fwd(q2.data_ptr(), k2.data_ptr(), v2.data_ptr(), buf2.data_ptr(), 1, 1, Nq2, Nk2, 64,
+                               q2.stride(0), q2.stride(1), 64, k2.stride(0), k2.stride(1), 64, v2.stride(0),
+                               v2.stride(1), 64, buf2.stride(0), buf2.stride(1), 64, 0.125, stream)
+    assert rc == 0, lib.cgs_last_error()
+    assert torch.equal(buf2[:, :Nq2, :64], n.attention(q2, k2, v2, 1))
+    assert (buf2[:, Nq2:, :] == SENT).all() and (buf2[:, :, 64:] == SENT).all()
+
+    # linear / GEGLU: M 200 (ragged row tile), N 96 (partial column tile), output with a wider leading dimension
+    M, K, Nn = 200, 64, 96
+    x, w, b = bf(randn((M, K), 7)), bf(randn((Nn, K), 8, 0.2)), bf(randn((Nn,), 9))
+    ld = Nn + 40
+    out = torch.full((M + 60, ld), SENT, dtype=torch.bfloat16, device="cuda")
+    rc = lib.cgs_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), None, out.data_ptr(), M, Nn, K, K, K, ld, 0, stream)
+    assert rc == 0, lib.cgs_last_error()
+    assert torch.equal(out[:M, :Nn], n.linear(x, w, b))
+    assert (out[M:] == SENT).all() and (out[:, Nn:] == SENT).all()
+    N2 = 128
+    w2, b2 = bf(randn((2 * N2, K), 10, 0.2)), bf(randn((2 * N2,), 11))
+    ld2 = N2 + 24
+    out2 = torch.full((M + 60, ld2), SENT, dtype=torch.bfloat16, device="cuda")
+    rc = lib.cgs_geglu_gemm_fwd(x.data_ptr(), w2.data_ptr(), b2.data_ptr(), out2.data_ptr(), M, N2, K, K, K, ld2, stream)
+    assert rc == 0, lib.cgs_last_error()
+    assert torch.equal(out2[:M, :N2], n.geglu(x, w2, b2))
+    assert (out2[M:] == SENT).all() and (out2[:, N2:] == SENT).all()
