@@ -311,6 +311,11 @@ def _group_norm_nhwc(x, weight, bias, groups, eps, silu, add_nc):
     return y
 
 
+# Switches for tools/ablation.py: each one sends an op back to the library call it replaced, so that the step-time value
+# of a kernel can be measured inside one process on one GPU (box-to-box variation is larger than most of them).
+FEATURES = {"residual_add": True, "cat_channels": True, "upsample2x": True, "fold_conv_bias": True}
+
+
 def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
     return (a.shape == b.shape and a.stride() == b.stride()
             and (a.is_contiguous() or (a.dim() == 4 and a.is_contiguous(memory_format=torch.channels_last))))
@@ -319,7 +324,7 @@ def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
 def residual_add(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
     """a + b (+ bias[None, :, None, None]) for bf16 CUDA tensors with one shared dense layout (contiguous or
     channels_last); anything else is a plain torch add (the reference's own path for this op)."""
-    if (a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and b.is_cuda
+    if (FEATURES["residual_add"] and a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and b.is_cuda
             and _same_dense_layout(a, b) and a.numel() % 8 == 0):
         channels, inner, bias_ptr = 0, 1, None
         if bias is not None:
@@ -354,6 +359,10 @@ def cat_channels(a: torch.Tensor, b: torch.Tensor, bias_a: Optional[torch.Tensor
                                    and _is_nhwc_bf16(a) and _is_nhwc_bf16(b)):
         a = a + bias_a.to(a.dtype).view(1, -1, 1, 1)
         bias_a = None
+    if not FEATURES["cat_channels"]:
+        if bias_a is not None:
+            a = a + bias_a.to(a.dtype).view(1, -1, 1, 1)
+        return torch.cat([a, b], dim=1)
     if (_is_nhwc_bf16(a) and _is_nhwc_bf16(b) and a.shape[0] == b.shape[0] and a.shape[2:] == b.shape[2:]
             and a.shape[1] % 8 == 0 and b.shape[1] % 8 == 0):
         n, ca, h, w = a.shape
@@ -370,7 +379,7 @@ def cat_channels(a: torch.Tensor, b: torch.Tensor, bias_a: Optional[torch.Tensor
 
 def upsample_nearest2x(x: torch.Tensor) -> torch.Tensor:
     """F.interpolate(x, scale 2, mode='nearest') for channels-last bf16 images; anything else is the torch call."""
-    if _is_nhwc_bf16(x) and x.shape[1] % 8 == 0:
+    if FEATURES["upsample2x"] and _is_nhwc_bf16(x) and x.shape[1] % 8 == 0:
         n, c, h, w = x.shape
         out = torch.empty((n, c, 2 * h, 2 * w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         with _Launch("upsample2x", x, 2.0 * 5 * x.numel()):

@@ -73,7 +73,8 @@ class Upsample(nn.Module):
             x = F.interpolate(x, size=shape, mode="nearest")
         if self.use_conv:
             conv = self.conv
-            if (bias_out is not None and x.is_cuda and x.dtype == torch.bfloat16 and hasattr(conv, "forward_nobias")
+            if (bias_out is not None and _native.FEATURES["fold_conv_bias"] and x.is_cuda
+                    and x.dtype == torch.bfloat16 and hasattr(conv, "forward_nobias")
                     and not conv.comfy_cast_weights and conv.bias is not None and conv.bias.dtype == torch.bfloat16):
                 bias_out.append(conv.bias)
                 return conv.forward_nobias(x)
@@ -123,7 +124,8 @@ class ResBlock(TimestepBlock):
         convs = [self.in_layers[2], self.out_layers[3]]
         if not isinstance(self.skip_connection, nn.Identity):
             convs.append(self.skip_connection)
-        return (x.is_cuda and x.dtype == torch.bfloat16 and hasattr(self.out_layers[0], "forward_fused")
+        return (_native.FEATURES["fold_conv_bias"] and x.is_cuda and x.dtype == torch.bfloat16
+                and hasattr(self.out_layers[0], "forward_fused")
                 and all(hasattr(c, "forward_nobias") and not c.comfy_cast_weights and c.bias is not None
                         and c.bias.dtype == torch.bfloat16 for c in convs))
 
