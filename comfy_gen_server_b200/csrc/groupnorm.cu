@@ -11,6 +11,17 @@
 
 namespace cgs {
 
+// x * sigmoid(x) = h + h * tanh(h), h = x / 2: one MUFU (tanh.approx, rel. error ~2^-11, below the bf16 rounding of the
+// result) and two FMA-pipe instructions. The IEEE division of x / (1 + exp(-x)) made the normalise kernels issue-bound
+// (~20 instructions per channel), and exp + reciprocal are two MUFUs per channel.
+__device__ __forceinline__ float silu_fast(float x) {
+    const float h = 0.5f * x;
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    return fmaf(h, t, h);
+}
+
+
 struct alignas(16) GN8 {
     __nv_bfloat162 v[4];
 };
@@ -91,8 +102,8 @@ groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __res
             const float2 f = __bfloat1622float2(a.v[j]);
             float v0 = fmaf(f.x, ga, be), v1 = fmaf(f.y, ga, be);
             if (SILU) {
-                v0 = v0 / (1.f + __expf(-v0));
-                v1 = v1 / (1.f + __expf(-v1));
+                v0 = silu_fast(v0);
+                v1 = silu_fast(v1);
             }
             o.v[j] = __floats2bfloat162_rn(v0, v1);
         }
@@ -169,17 +180,39 @@ gn_nhwc_stats_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 #pragma unroll
         for (int j = 0; j < 4; ++j) e[j] = ev.v[j];
     }
-    float sa = 0.f, qa = 0.f, sb = 0.f, qb = 0.f;
+    // one (sum, sum of squares) pair per channel of the vector: four shared accumulators were four dependent FADD
+    // chains of length 8 per 16 bytes, which capped the kernel at half of HBM speed
+    float sj[8], qj[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sj[j] = qj[j] = 0.f;
     const int r_begin = chunk * rows_per_chunk;
     const int r_end = min(HW, r_begin + rows_per_chunk);
-    for (int r = r_begin + rsub; r < r_end; r += rows_per_iter) {
-        float f[8];
-        gn_load_row_vec(x + ((size_t)n * HW + r) * C + c0, e, has_add, f);
+    const __nv_bfloat16* xn = x + (size_t)n * HW * C + c0;
+    auto accumulate = [&](GN8 a) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            if (j < split) { sa += f[j]; qa += f[j] * f[j]; }
-            else           { sb += f[j]; qb += f[j] * f[j]; }
+        for (int j = 0; j < 4; ++j) {
+            if (has_add) a.v[j] = __hadd2_rn(a.v[j], e[j]);      // bf16 add, as the reference's h + emb
+            const float2 t = __bfloat1622float2(a.v[j]);
+            sj[2 * j] += t.x;
+            qj[2 * j] = fmaf(t.x, t.x, qj[2 * j]);
+            sj[2 * j + 1] += t.y;
+            qj[2 * j + 1] = fmaf(t.y, t.y, qj[2 * j + 1]);
         }
+    };
+    int r = r_begin + rsub;
+    for (; r + 3 * rows_per_iter < r_end; r += 4 * rows_per_iter) {      // four rows per trip, loads first
+        GN8 raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) raw[u] = *reinterpret_cast<const GN8*>(xn + (size_t)(r + u * rows_per_iter) * C);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) accumulate(raw[u]);
+    }
+    for (; r < r_end; r += rows_per_iter) accumulate(*reinterpret_cast<const GN8*>(xn + (size_t)r * C));
+    float sa = 0.f, qa = 0.f, sb = 0.f, qb = 0.f;       // channels [0, split) belong to group g0, the rest to g0 + 1
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (j < split) { sa += sj[j]; qa += qj[j]; }
+        else           { sb += sj[j]; qb += qj[j]; }
     }
     part[threadIdx.x][0] = sa;
     part[threadIdx.x][1] = qa;
@@ -256,23 +289,35 @@ gn_nhwc_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
     }
     const int r_begin = chunk * rows_per_chunk;
     const int r_end = min(HW, r_begin + rows_per_chunk);
-    for (int r = r_begin + rsub; r < r_end; r += rows_per_iter) {
-        float f[8];
-        const size_t off = ((size_t)n * HW + r) * C + c0;
-        gn_load_row_vec(x + off, e, has_add, f);
+    auto finish = [&](GN8 a, size_t off) {
         GN8 o;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            float v0 = fmaf(f[2 * j], ga[2 * j], be[2 * j]);
-            float v1 = fmaf(f[2 * j + 1], ga[2 * j + 1], be[2 * j + 1]);
+            if (has_add) a.v[j] = __hadd2_rn(a.v[j], e[j]);      // bf16 add, as the reference's h + emb
+            const float2 t = __bfloat1622float2(a.v[j]);
+            float v0 = fmaf(t.x, ga[2 * j], be[2 * j]);
+            float v1 = fmaf(t.y, ga[2 * j + 1], be[2 * j + 1]);
             if (SILU) {
-                v0 = v0 / (1.f + __expf(-v0));
-                v1 = v1 / (1.f + __expf(-v1));
+                v0 = silu_fast(v0);
+                v1 = silu_fast(v1);
             }
             o.v[j] = __floats2bfloat162_rn(v0, v1);
         }
         *reinterpret_cast<GN8*>(y + off) = o;
+    };
+    // four rows per trip, loads first (memory-level parallelism: see the statistics kernel)
+    const size_t base = (size_t)n * HW * C + c0;
+    int r = r_begin + rsub;
+    for (; r + 3 * rows_per_iter < r_end; r += 4 * rows_per_iter) {
+        GN8 raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            raw[u] = *reinterpret_cast<const GN8*>(x + base + (size_t)(r + u * rows_per_iter) * C);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) finish(raw[u], base + (size_t)(r + u * rows_per_iter) * C);
     }
+    for (; r < r_end; r += rows_per_iter)
+        finish(*reinterpret_cast<const GN8*>(x + base + (size_t)r * C), base + (size_t)r * C);
 }
 
 }  // namespace cgs
