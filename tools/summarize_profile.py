@@ -10,7 +10,7 @@ tag = sys.argv[1]
 SHAPES = [
     ("gemm_kernel<1>", "GEGLU GEMM M=65536 K=640 N=2560 (2N=5120)", 425984000, 429496729600.0),
     ("gemm_kernel<0>", "linear+residual (ff.net.2) M=65536 K=2560 N=640", 506593280, 214748364800.0),
-    ("attn_fwd_kernel<1, 2, 3", "self-attention B2=16 H=10 N=4096 d=64", 335544320, 687194767360.0),
+    ("attn_fwd_kernel<1, 3, 4", "self-attention B2=16 H=10 N=4096 d=64", 335544320, 687194767360.0),
     ("attn_fwd_kernel<1, 1, 1", "cross-attention B2=16 H=10 Nq=4096 Nk=77 d=64", 170926080, 12918456320.0),
 ]
 
