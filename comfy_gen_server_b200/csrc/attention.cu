@@ -636,7 +636,20 @@ static int attention_entry(const void* q, const void* k, const void* v, void* ou
     }
     AttnParams p;
     p.dbg = nullptr;
-    if (const char* e = getenv("CGS_ATTN_TRACE")) p.dbg = reinterpret_cast<long long*>(strtoull(e, nullptr, 0));
+    // developer knobs, read once per process (tools/attn_trace*.py, tools/kernel_bench.py set them before the first call)
+    static const struct Knobs {
+        long long* trace;
+        int max_1cta;
+        bool no_3tile;
+        Knobs() {
+            const char* e = getenv("CGS_ATTN_TRACE");
+            trace = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
+            e = getenv("CGS_ATTN_MAX_TILES_1CTA");
+            max_1cta = e ? atoi(e) : 8;
+            no_3tile = getenv("CGS_ATTN_NO_3TILE") != nullptr;
+        }
+    } knobs;
+    p.dbg = knobs.trace;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.o_stride_b = o_stride_b;
     p.o_stride_n = o_stride_n;
@@ -658,11 +671,10 @@ static int attention_entry(const void* q, const void* k, const void* v, void* ou
     // barrier latencies of one another. d <= 128: two query tiles against 128-key tiles. Short key sequences (text
     // cross-attention, up to 8 key tiles): one tile per CTA, 256 TMEM columns, two CTAs per SM, so the set-up and
     // epilogue of one CTA overlap the loop of the other.
-    int max_1cta = 8;
-    if (const char* e = getenv("CGS_ATTN_MAX_TILES_1CTA")) max_1cta = atoi(e);   // experiment knob
+    const int max_1cta = knobs.max_1cta;
     const bool multi = Nq > attn::BLOCK_M && n_tiles > max_1cta && mask == nullptr;   // masked: one-tile variants only
     int nqt = 1, bn = 128;
-    if (multi && d <= 64 && !getenv("CGS_ATTN_NO_3TILE")) { nqt = 3; bn = 64; }
+    if (multi && d <= 64 && !knobs.no_3tile) { nqt = 3; bn = 64; }
     else if (multi && 2 * (192 + dv_n) <= 512) { nqt = 2; }
     int cols = 32;
     while (cols < nqt * (bn + bn / 2 + dv_n)) cols *= 2;

@@ -365,8 +365,10 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
         int rc = make_tmap_bf16(&tmO, out, 2, dims, strides, box);
         if (rc != kOk) return rc;
     }
-    const char* dbg_env = getenv("CGS_GEMM_DEBUG");
-    const int dbg = dbg_env ? atoi(dbg_env) : 0;
+    static const int dbg = [] {                 // developer knob (tools/gemm_dbg.sh), read once per process
+        const char* e = getenv("CGS_GEMM_DEBUG");
+        return e ? atoi(e) : 0;
+    }();
     const int tiles_m = (int)((M + BM - 1) / BM);
     const int tiles_n = (epi == EPI_GEGLU) ? N / BN_HALF : (N + UMMA_N - 1) / UMMA_N;
     const long long tiles = (long long)tiles_m * tiles_n;

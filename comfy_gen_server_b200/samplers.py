@@ -508,13 +508,21 @@ class CFGGuider:
         st["calls"] += 1
         if st["graph"] is None and st["calls"] == 1 and st["graph_opt"] not in (False, None):
             st["graph"] = self._reuse_step_graph(st, x, model_options)      # captured by an earlier sample() call?
+            if st["graph"] is None and st["graph_opt"] == "auto" and type(self) is CFGGuider:
+                # an earlier call already found the GPU to be the limiter for these shapes: do not probe again
+                verdicts = self.inner_model.__dict__.get("_step_graph_verdicts", {})
+                if verdicts.get(self._graph_key(st, x, model_options)) is False:
+                    st["graph"] = False
         if st["graph"] is None and st["calls"] >= 3:
             st["graph"] = self._maybe_capture_step(st, x, model_options)
         if st["graph"]:
             return self._graph_step(st, x, i, sigma_f, sampler, c0, c1, c2, c3, old_denoised)
         # (the first step also pays one-time costs -- cross-attention K/V, cuDNN plan selection -- so the second is probed)
-        probe = st["calls"] == 2 and st["graph_opt"] == "auto"
+        probe = st["calls"] == 2 and st["graph_opt"] == "auto" and st["graph"] is None
         if probe:
+            # with work still queued on the GPU the launch queue fills up and the host's enqueue time reads as the
+            # GPU's: drain it once (once per model and shape, the verdict is remembered)
+            torch.cuda.synchronize()
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()
             t_host = time.perf_counter()
@@ -553,7 +561,9 @@ class CFGGuider:
                 return False
             host_ms, ev = st["probe"]
             ev[1].synchronize()
-            if host_ms < 0.8 * ev[0].elapsed_time(ev[1]):      # the GPU is the limiter: nothing to gain
+            host_bound = host_ms >= 0.8 * ev[0].elapsed_time(ev[1])
+            self.inner_model.__dict__.setdefault("_step_graph_verdicts", {})[self._graph_key(st, x, model_options)] = host_bound
+            if not host_bound:                                  # the GPU is the limiter: nothing to gain
                 return False
         try:
             return self._capture_step(st, x, model_options)
