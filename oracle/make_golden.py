@@ -264,11 +264,44 @@ def gen_e2e(family, seed, batch, hw, steps, sampler, scheduler, pos_len, neg_len
     save(name, **arrays)
 
 
+def gen_workflows():
+    """The sampling node's other call shapes (nodes.py:1420-1439, 1753-1785), each through comfy.sample.sample as
+    common_ksampler drives it: img2img (denoise < 1), a KSamplerAdvanced window with and without leftover noise,
+    in-painting (noise_mask) and per-image noise (batch_index)."""
+    family, seed, hw, steps = "tiny_sd15", 45, 16, 10
+    ctx_dim = uc.FAMILIES[family]["unet"]["context_dim"]
+    patcher, model = build_reference_model(family, seed)
+    pos, neg = randn((1, 77, ctx_dim), seed + 1), randn((1, 77, ctx_dim), seed + 2)
+    positive, negative = [[pos, {}]], [[neg, {}]]
+    image = randn((2, 4, hw, hw), seed + 5, 0.8)
+    mask = torch.zeros(2, 1, hw, hw)
+    mask[:, :, :, hw // 2:] = 1.0
+    run = lambda noise, latent, **kw: comfy.sample.sample(patcher, noise, steps, 7.0, "euler", "normal", positive, negative,
+                                                         latent, seed=seed, disable_pbar=True, **kw)
+    out = dict(positive=pos, negative=neg, image=image, mask=mask, seed=np.int64(seed), steps=np.int64(steps))
+    with torch.inference_mode():
+        noise = comfy.sample.prepare_noise(image, seed)
+        out["img2img_denoise06"] = run(noise, image, denoise=0.6)
+        zeros = torch.zeros_like(image)
+        out["advanced_3_7_leftover"] = run(zeros, image, disable_noise=True, start_step=3, last_step=7,
+                                           force_full_denoise=False)
+        out["advanced_0_6_full"] = run(noise, image, start_step=0, last_step=6, force_full_denoise=True)
+        out["inpaint"] = run(noise, image, noise_mask=mask)
+        inds = [3, 1]
+        out["batch_index_noise"] = comfy.sample.prepare_noise(image, seed, inds)
+        out["batch_index"] = run(out["batch_index_noise"], torch.zeros_like(image))
+    save("workflows_tiny_sd15", **out)
+
+
 def main():
     torch.manual_seed(0)
+    if "--only-workflows" in sys.argv:
+        gen_workflows()
+        return
     gen_attention()
     if "--only-attention" in sys.argv:
         return
+    gen_workflows()
     gen_blocks()
     gen_schedules()
     gen_sampler_kat()

@@ -419,13 +419,31 @@ def sdxl_adm(pooled: Tensor, height: int, width: int) -> Tensor:
 def sample(cfg: dict, sd: Dict[str, Tensor], prediction: str, scale_factor: float, noise: Tensor, steps: int,
            cond_scale: float, sampler: str, scheduler: str, positive: Tensor, negative: Tensor,
            latent: Tensor, pooled_pos: Optional[Tensor] = None, pooled_neg: Optional[Tensor] = None,
-           callback=None, max_steps: Optional[int] = None) -> Tensor:
-    """comfy.sample.sample -> KSampler -> CFGGuider -> KSAMPLER -> sample_<name> with plain conds."""
+           callback=None, max_steps: Optional[int] = None, denoise: Optional[float] = None,
+           start_step: Optional[int] = None, last_step: Optional[int] = None, force_full_denoise: bool = False,
+           noise_mask: Optional[Tensor] = None) -> Tensor:
+    """comfy.sample.sample -> KSampler -> CFGGuider -> KSAMPLER -> sample_<name> with plain conds.
+    denoise / start_step / last_step / force_full_denoise: KSampler.set_steps and KSampler.sample
+    (comfy/samplers.py:716-755); noise_mask: KSamplerX0Inpaint (comfy/samplers.py:262-275)."""
     table = discrete_sigmas()
     log_table = discrete_log_sigmas()
-    sigmas = calculate_sigmas(table, scheduler, steps, log_table)
+    if denoise is None or denoise > 0.9999:
+        sigmas = calculate_sigmas(table, scheduler, steps, log_table)
+    elif denoise <= 0.0:
+        return latent
+    else:
+        sigmas = calculate_sigmas(table, scheduler, int(steps / denoise), log_table)[-(steps + 1):]
     if max_steps is not None:
         sigmas = sigmas[:max_steps + 1]
+    if last_step is not None and last_step < len(sigmas) - 1:
+        sigmas = sigmas[:last_step + 1].clone()
+        if force_full_denoise:
+            sigmas[-1] = 0
+    if start_step is not None:
+        if start_step < len(sigmas) - 1:
+            sigmas = sigmas[start_step:]
+        else:
+            return latent
     extra_c = extra_u = None
     if cfg.get('adm_in_channels'):
         h8, w8 = noise.shape[2] * 8, noise.shape[3] * 8
@@ -445,5 +463,13 @@ def sample(cfg: dict, sd: Dict[str, Tensor], prediction: str, scale_factor: floa
         latent = latent * scale_factor
     max_denoise = math.isclose(float(table[-1]), float(sigmas[0]), rel_tol=1e-5) or float(sigmas[0]) > float(table[-1])
     x = noise_scaling(sigmas[0], noise, latent, max_denoise)
-    x = SAMPLERS[sampler](model, x, sigmas, callback)
+    denoiser = model
+    if noise_mask is not None:
+        keep = 1.0 - noise_mask
+
+        def denoiser(x_in, sigma):       # KSamplerX0Inpaint: the kept region follows the noised input image
+            shaped = sigma.reshape([sigma.shape[0]] + [1] * (noise.dim() - 1))
+            x_in = x_in * noise_mask + noise_scaling(shaped, noise, latent, False) * keep
+            return model(x_in, sigma) * noise_mask + latent * keep
+    x = SAMPLERS[sampler](denoiser, x, sigmas, callback)
     return x / scale_factor

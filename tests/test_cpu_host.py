@@ -244,3 +244,18 @@ print("OK")
     import subprocess
     p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert p.returncode == 0 and "OK" in p.stdout, p.stdout[-1500:] + p.stderr[-1500:]
+
+
+def test_sampler_nodes_surface():
+    """nodes.py:1441-1465, 1753-1785: class attributes and INPUT_TYPES the UI / workflow JSONs rely on."""
+    from comfy_gen_server_b200 import nodes, samplers
+    for cls in (nodes.KSampler, nodes.KSamplerAdvanced):
+        assert cls.RETURN_TYPES == ("LATENT",) and cls.FUNCTION == "sample" and cls.CATEGORY == "sampling"
+    req = nodes.KSampler.INPUT_TYPES()["required"]
+    assert list(req) == ["model", "seed", "steps", "cfg", "sampler_name", "scheduler", "positive", "negative",
+                         "latent_image", "denoise"]
+    assert req["sampler_name"][0] is samplers.KSampler.SAMPLERS and req["seed"][1]["max"] == 0xffffffffffffffff
+    adv = nodes.KSamplerAdvanced.INPUT_TYPES()["required"]
+    assert list(adv) == ["model", "add_noise", "noise_seed", "steps", "cfg", "sampler_name", "scheduler", "positive",
+                         "negative", "latent_image", "start_at_step", "end_at_step", "return_with_leftover_noise"]
+    assert nodes.NODE_CLASS_MAPPINGS["KSampler"] is nodes.KSampler

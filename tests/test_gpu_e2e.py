@@ -248,6 +248,43 @@ def test_cuda_graph_is_reused_across_sample_calls_with_new_prompts():
     assert not torch.equal(want[0], want[1])
 
 
+def test_sampler_nodes_workflow_variants_vs_reference():
+    """nodes.KSampler / KSamplerAdvanced (LATENT dicts in and out) against the reference's comfy.sample.sample for the
+    other shapes of the call: img2img (denoise 0.6), an advanced window without added noise that keeps the leftover
+    noise, a window with full denoise, in-painting with a noise_mask, and batch_index noise."""
+    from comfy_gen_server_b200 import nodes, sample as S
+    g = load_golden("workflows_tiny_sd15")
+    seed, steps = int(g["seed"]), int(g["steps"])
+    patcher = _patcher("tiny_sd15", seed)
+    pos, neg = [[g["positive"], {}]], [[g["negative"], {}]]
+    image = g["image"]
+    ks, ka = nodes.KSampler(), nodes.KSamplerAdvanced()
+    assert set(nodes.KSampler.INPUT_TYPES()["required"]) == {"model", "seed", "steps", "cfg", "sampler_name", "scheduler",
+                                                             "positive", "negative", "latent_image", "denoise"}
+    with torch.inference_mode():
+        got = {
+            "img2img_denoise06": ks.sample(patcher, seed, steps, 7.0, "euler", "normal", pos, neg, {"samples": image}, 0.6),
+            "advanced_3_7_leftover": ka.sample(patcher, "disable", seed, steps, 7.0, "euler", "normal", pos, neg,
+                                               {"samples": image}, 3, 7, "enable"),
+            "advanced_0_6_full": ka.sample(patcher, "enable", seed, steps, 7.0, "euler", "normal", pos, neg,
+                                           {"samples": image}, 0, 6, "disable"),
+            "inpaint": ks.sample(patcher, seed, steps, 7.0, "euler", "normal", pos, neg,
+                                 {"samples": image, "noise_mask": g["mask"]}, 1.0),
+            "batch_index": ks.sample(patcher, seed, steps, 7.0, "euler", "normal", pos, neg,
+                                     {"samples": torch.zeros_like(image), "batch_index": [3, 1]}, 1.0),
+        }
+    assert torch.equal(S.prepare_noise(image, seed, [3, 1]), g["batch_index_noise"])
+    for name, (out,) in got.items():
+        assert set(out) >= {"samples"} and out["samples"].shape == image.shape
+        c = cosine(out["samples"].float().cpu(), g[name])
+        print(f"{name}: cosine {c:.6f}")
+        assert c > 0.999, (name, c)
+    assert "noise_mask" in got["inpaint"][0]                      # the LATENT dict is copied through
+    # the in-painted result keeps the unmasked half of the input image (mask 0 = keep)
+    kept = got["inpaint"][0]["samples"].float().cpu()[:, :, :, :image.shape[-1] // 2]
+    assert (kept - image[:, :, :, :image.shape[-1] // 2]).abs().max() < 1e-4
+
+
 def test_channels_last_pipeline_matches_nchw_pipeline():
     """the NHWC end-to-end UNet (channels_last GroupNorm kernels, cuDNN NHWC convs, free token views)
     gives the same latents as the NCHW pipeline."""

@@ -156,3 +156,26 @@ def test_end_to_end_tiny_matches_reference(family, name, hw, steps, sampler, sch
     assert cosine(den[0], g["denoised_first"]) > 0.999999
     assert cosine(out, g["final"]) > 0.99999
     assert (out - g["final"]).abs().max() < 2e-3 * float(g["final"].abs().max())
+
+
+def test_workflow_variants_match_reference():
+    """denoise < 1, KSamplerAdvanced windows, in-painting mask, batch_index noise: oracle.sample against the
+    reference's comfy.sample.sample on the tiny SD1.5 UNet (fp32 CPU both)."""
+    g = load_golden("workflows_tiny_sd15")
+    fam = uc.FAMILIES["tiny_sd15"]
+    seed, steps = int(g["seed"]), int(g["steps"])
+    sd = uc.seeded_state_dict(uc.param_shapes(fam["unet"]), seed)
+    image = g["image"]
+    noise = O.prepare_noise(image, seed)
+    run = lambda n, lat, **kw: O.sample(fam["unet"], sd, fam["prediction"], fam["scale_factor"], n, steps, 7.0,
+                                        "euler", "normal", g["positive"], g["negative"], lat, **kw)
+    cases = {
+        "img2img_denoise06": run(noise, image, denoise=0.6),
+        "advanced_3_7_leftover": run(torch.zeros_like(image), image, start_step=3, last_step=7),
+        "advanced_0_6_full": run(noise, image, start_step=0, last_step=6, force_full_denoise=True),
+        "inpaint": run(noise, image, noise_mask=g["mask"]),
+        "batch_index": run(g["batch_index_noise"], torch.zeros_like(image)),
+    }
+    for name, out in cases.items():
+        err = (out - g[name]).abs().max().item()
+        assert err < 5e-4 * max(1.0, float(g[name].abs().max())), (name, err)
