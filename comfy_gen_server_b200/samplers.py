@@ -627,7 +627,11 @@ class CFGGuider:
         return (tuple(x.shape), str(x.device), st["copies"], tuple(st["cond_or_uncond"]), float(self.cfg),
                 m.model_sampling.pred_type, float(m.model_sampling.sigma_data), tuple(st["context"].shape),
                 None if st["y"] is None else tuple(st["y"].shape), tuple(sorted(map(str, topt.keys()))),
-                len(params), weights)
+                len(params), weights,
+                # the code the capture recorded: feature switches and the op bindings (tools and tests rebind them)
+                tuple(sorted(_native.FEATURES.items())),
+                tuple(id(getattr(_native, f)) for f in ("attention", "layer_norm", "add_layer_norm_", "group_norm",
+                                                        "geglu", "linear", "residual_add", "cat_channels")))
 
     def _cross_attention_modules(self):
         from .attention import CrossAttention

