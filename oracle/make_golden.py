@@ -293,8 +293,34 @@ def gen_workflows():
     save("workflows_tiny_sd15", **out)
 
 
+def gen_sdxl_headline(seed=46, hw=128, steps=30, first_steps=2):
+    """The headline configuration at full size (BASELINE.json configs[2]: SDXL 1024^2, DPM++ 2M Karras, CFG 7; one
+    image): the first `first_steps` steps of the 30-step schedule through the reference's fp32 CPU path
+    (comfy.sample.sample with last_step), which pins the full-size network and the multistep update."""
+    fam = uc.FAMILIES["sdxl"]
+    ctx_dim = fam["unet"]["context_dim"]
+    patcher, model = build_reference_model("sdxl", seed)
+    latent = torch.zeros(1, 4, hw, hw)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    pos, neg = randn((1, 77, ctx_dim), seed + 1), randn((1, 77, ctx_dim), seed + 2)
+    pp, pn = randn((1, 1280), seed + 3), randn((1, 1280), seed + 4)
+    t0 = time.time()
+    with torch.inference_mode():
+        out = comfy.sample.sample(patcher, noise, steps, 7.0, "dpmpp_2m", "karras", [[pos, {"pooled_output": pp}]],
+                                  [[neg, {"pooled_output": pn}]], latent, seed=seed, disable_pbar=True,
+                                  last_step=first_steps, force_full_denoise=False)
+    dt = time.time() - t0
+    print(f"e2e_sdxl_headline: reference ran {first_steps} of {steps} steps in {dt:.1f}s; out std {out.std():.4f}")
+    save("e2e_sdxl_headline_2steps", x_after=out, noise=noise, positive=pos, negative=neg, pooled_pos=pp, pooled_neg=pn,
+         seed=np.int64(seed), steps=np.int64(steps), first_steps=np.int64(first_steps), ref_seconds=np.float64(dt),
+         ref_threads=np.int64(torch.get_num_threads()))
+
+
 def main():
     torch.manual_seed(0)
+    if "--only-sdxl-headline" in sys.argv:
+        gen_sdxl_headline()
+        return
     if "--only-workflows" in sys.argv:
         gen_workflows()
         return
@@ -309,6 +335,8 @@ def main():
     gen_e2e("tiny_sd15", 42, 2, 16, 20, "euler", "normal", 77, 77, "e2e_tiny_sd15_euler")
     gen_e2e("tiny_sd21v", 43, 2, 12, 25, "euler", "normal", 77, 154, "e2e_tiny_sd21v_euler")
     gen_e2e("tiny_sdxl", 44, 2, 16, 30, "dpmpp_2m", "karras", 77, 77, "e2e_tiny_sdxl_dpmpp2m")
+    if "--skip-sdxl" not in sys.argv:
+        gen_sdxl_headline()
     if "--skip-sd15" not in sys.argv:
         # BASELINE.json configs[0]: SD1.5 512x512 batch 1, 20-step Euler, CFG 7.0, CPU reference path
         gen_e2e("sd15", 42, 1, 64, 20, "euler", "normal", 77, 77, "e2e_sd15_config1")

@@ -248,6 +248,29 @@ def test_cuda_graph_is_reused_across_sample_calls_with_new_prompts():
     assert not torch.equal(want[0], want[1])
 
 
+def test_headline_config_sdxl_full_size_first_steps_vs_reference():
+    """BASELINE.json configs[2] at full size (SDXL 1024^2, DPM++ 2M Karras, CFG 7, one image): the first two steps of
+    the 30-step schedule against the reference's fp32 CPU run (76.6 s on 8 cores), incl. the first multistep update."""
+    from comfy_gen_server_b200 import sample as S
+    g = load_golden("e2e_sdxl_headline_2steps")
+    seed, steps, first = int(g["seed"]), int(g["steps"]), int(g["first_steps"])
+    patcher = _patcher("sdxl", seed)
+    latent = torch.zeros(1, 4, 128, 128)
+    noise = S.prepare_noise(latent, seed)
+    assert torch.equal(noise, g["noise"])
+    pos = [[g["positive"], {"pooled_output": g["pooled_pos"]}]]
+    neg = [[g["negative"], {"pooled_output": g["pooled_neg"]}]]
+    with torch.inference_mode():
+        out = S.sample(patcher, noise, steps, 7.0, "dpmpp_2m", "karras", pos, neg, latent, seed=seed,
+                       last_step=first, force_full_denoise=False).float().cpu()
+    c = cosine(out, g["x_after"])
+    rel = float((out - g["x_after"]).abs().max() / g["x_after"].abs().max())
+    print(f"SDXL 1024^2 after {first} of {steps} steps: cosine {c:.6f}, max rel err {rel:.4f}")
+    assert torch.isfinite(out).all() and c > 0.999
+    del patcher
+    torch.cuda.empty_cache()
+
+
 def test_sampler_nodes_workflow_variants_vs_reference():
     """nodes.KSampler / KSamplerAdvanced (LATENT dicts in and out) against the reference's comfy.sample.sample for the
     other shapes of the call: img2img (denoise 0.6), an advanced window without added noise that keeps the leftover
