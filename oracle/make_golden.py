@@ -316,8 +316,31 @@ def gen_sdxl_headline(seed=46, hw=128, steps=30, first_steps=2):
          ref_threads=np.int64(torch.get_num_threads()))
 
 
+def gen_sd21v_full(seed=47, hw=96, steps=25, first_steps=3):
+    """BASELINE.json configs[3] at full size (SD2.1-v 768^2, Euler / normal, CFG 7, v-prediction; one image): the first
+    steps through the reference's fp32 CPU path. Token counts 9216 / 2304 / 576 / 144 are not multiples of 128."""
+    fam = uc.FAMILIES["sd21v"]
+    ctx_dim = fam["unet"]["context_dim"]
+    patcher, model = build_reference_model("sd21v", seed)
+    latent = torch.zeros(1, 4, hw, hw)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    pos, neg = randn((1, 77, ctx_dim), seed + 1), randn((1, 77, ctx_dim), seed + 2)
+    t0 = time.time()
+    with torch.inference_mode():
+        out = comfy.sample.sample(patcher, noise, steps, 7.0, "euler", "normal", [[pos, {}]], [[neg, {}]], latent,
+                                  seed=seed, disable_pbar=True, last_step=first_steps, force_full_denoise=False)
+    dt = time.time() - t0
+    print(f"e2e_sd21v_full: reference ran {first_steps} of {steps} steps in {dt:.1f}s; out std {out.std():.4f}")
+    save("e2e_sd21v_full_3steps", x_after=out, noise=noise, positive=pos, negative=neg, seed=np.int64(seed),
+         steps=np.int64(steps), first_steps=np.int64(first_steps), ref_seconds=np.float64(dt),
+         ref_threads=np.int64(torch.get_num_threads()))
+
+
 def main():
     torch.manual_seed(0)
+    if "--only-sd21v-full" in sys.argv:
+        gen_sd21v_full()
+        return
     if "--only-sdxl-headline" in sys.argv:
         gen_sdxl_headline()
         return
@@ -337,6 +360,7 @@ def main():
     gen_e2e("tiny_sdxl", 44, 2, 16, 30, "dpmpp_2m", "karras", 77, 77, "e2e_tiny_sdxl_dpmpp2m")
     if "--skip-sdxl" not in sys.argv:
         gen_sdxl_headline()
+        gen_sd21v_full()
     if "--skip-sd15" not in sys.argv:
         # BASELINE.json configs[0]: SD1.5 512x512 batch 1, 20-step Euler, CFG 7.0, CPU reference path
         gen_e2e("sd15", 42, 1, 64, 20, "euler", "normal", 77, 77, "e2e_sd15_config1")

@@ -271,6 +271,25 @@ def test_headline_config_sdxl_full_size_first_steps_vs_reference():
     torch.cuda.empty_cache()
 
 
+def test_config4_sd21v_full_size_first_steps_vs_reference():
+    """BASELINE.json configs[3] at full size (SD2.1-v 768^2, v-prediction, Euler / normal; token counts 9216 / 2304 / 576 /
+    144): the first three of 25 steps against the reference's fp32 CPU run."""
+    from comfy_gen_server_b200 import sample as S
+    g = load_golden("e2e_sd21v_full_3steps")
+    seed, steps, first = int(g["seed"]), int(g["steps"]), int(g["first_steps"])
+    patcher = _patcher("sd21v", seed)
+    latent = torch.zeros(1, 4, 96, 96)
+    noise = S.prepare_noise(latent, seed)
+    with torch.inference_mode():
+        out = S.sample(patcher, noise, steps, 7.0, "euler", "normal", [[g["positive"], {}]], [[g["negative"], {}]], latent,
+                       seed=seed, last_step=first, force_full_denoise=False).float().cpu()
+    c = cosine(out, g["x_after"])
+    print(f"SD2.1-v 768^2 after {first} of {steps} steps: cosine {c:.6f}")
+    assert torch.isfinite(out).all() and c > 0.999
+    del patcher
+    torch.cuda.empty_cache()
+
+
 def test_sampler_nodes_workflow_variants_vs_reference():
     """nodes.KSampler / KSamplerAdvanced (LATENT dicts in and out) against the reference's comfy.sample.sample for the
     other shapes of the call: img2img (denoise 0.6), an advanced window without added noise that keeps the leftover
