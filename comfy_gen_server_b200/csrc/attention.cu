@@ -38,6 +38,8 @@
 
 #include <stdlib.h>
 
+#include <type_traits>
+
 namespace cgs {
 
 namespace attn {
@@ -380,7 +382,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         float m_run = -INFINITY;  // running max, already multiplied by scale_log2
         float m_raw = -INFINITY;  // the same before scaling (used by the masked variant only)
         float l_run = 0.f;        // row sum
-        for (int j = 0; j < n_tiles; ++j, ++g) {
+        // One key tile. The last tile of a key sequence that is not a multiple of the tile width is a second instance
+        // of this body with the masking code in it: the loop over full tiles carries none of it.
+        auto key_tile = [&](auto ragged_tag, int j) {
+            constexpr bool RAGGED = decltype(ragged_tag)::value;
             CGS_TRACE(t, g, 0);
             mbar_wait(&s_full[t], g & 1);
             CGS_TRACE(t, g, 1);
@@ -406,7 +411,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     if (i < n_valid)
                         sr[i] = __float_as_uint(fmaf(__ldg(mrow + i), p.inv_scale, __uint_as_float(sr[i])));
             }
-            if (n_valid < COLS) {
+            if constexpr (RAGGED) {
 #pragma unroll
                 for (int i = 0; i < COLS; ++i)
                     if (i >= n_valid) sr[i] = 0xff800000u;  // -inf
@@ -493,6 +498,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tc_fence_before();
             mbar_arrive(&p_full[t]);
             CGS_TRACE(t, g, 5);
+        };
+        const int n_full = p.Nk / BLOCK_N;
+        for (int j = 0; j < n_full; ++j, ++g) key_tile(std::false_type{}, j);
+        if (n_full < n_tiles) {
+            key_tile(std::true_type{}, n_full);
+            ++g;
         }
 
         // epilogue: O / l -> bf16 -> global. (The next item's first PV, which overwrites O, is issued only after
