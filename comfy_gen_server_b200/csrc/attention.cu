@@ -427,18 +427,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             float mx = fmaxf(fmax3(mx0, mx1, mx2), mx3);
             const float m_new = mx * scale;
 
-            float alpha = 1.f;
-            bool need_rescale = false;
-            if (j == 0) {
-                m_run = m_new;
-                m_raw = mx;
-            } else if (m_new > m_run + kRescaleThreshold) {
-                alpha = ex2_approx(m_run - m_new);
-                l_run *= alpha;
-                m_run = m_new;
-                m_raw = mx;
-                need_rescale = true;
-            }
+            // lazy running max, branch-free (a per-thread branch here put a reconvergence point between the max and
+            // the exponentials): the reference point moves only when the tile's max exceeds it by > 2^8, or on the
+            // item's first tile (m_run = -inf, alpha = 2^-inf = 0, l_run = 0)
+            const bool grow = (j == 0) || (m_new > m_run + kRescaleThreshold);
+            const float m_next = grow ? m_new : m_run;
+            const float alpha = ex2_approx(m_run - m_next);         // 1 when the reference point stays
+            const bool need_rescale = grow && j > 0;
+            l_run *= alpha;
+            m_run = m_next;
+            m_raw = grow ? mx : m_raw;
             const uint64_t negm2 = pack_f32x2(-m_run, -m_run);
             // masked variant: x = (s - m) * scale, subtraction first. With s * scale - m * scale in one FMA the
             // rounding of m * scale (half an ulp of m) is left in x; harmless for |m| ~ 10, an overflow for a row
