@@ -168,8 +168,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
         if (clock64() - t0 > 8000000000LL) {
+#ifdef CGS_MBAR_DEBUG     // (a printf is an ABI call inside the hot kernels: only in debug builds)
             printf("cgs: mbarrier watchdog: block (%d,%d,%d) thread %d bar smem 0x%x parity %u\n",
                    blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+#endif
             __trap();
         }
     }
@@ -208,8 +210,10 @@ __device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity)
             if (mbar_try_wait(bar, parity)) return;
         }
         if (clock64() - t0 > 8000000000LL) {
+#ifdef CGS_MBAR_DEBUG
             printf("cgs: mbarrier watchdog: block (%d,%d,%d) thread %d bar smem 0x%x parity %u\n",
                    blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+#endif
             __trap();
         }
     }
