@@ -473,12 +473,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 unpack_f32x2(acc1, s2, s3);
                 l_run += (s0 + s1) + (s2 + s3);
             }
-            if (g > 0) {
-                // PV of the previous key tile must have finished reading P (and O must be quiescent for a rescale).
-                // It was issued a whole softmax ago, so this wait is normally already satisfied.
-                mbar_wait(&o_full[t], (g - 1) & 1);
-                tc_fence_after();
-            }
+            // PV of the previous key tile must have finished reading P (and O must be quiescent for a rescale). It was
+            // issued a whole softmax ago, so this wait is normally already satisfied. (For g == 0 it asks for the phase
+            // before the first one, which an initialised barrier reports as complete: no special case.)
+            mbar_wait(&o_full[t], (g - 1) & 1);
+            tc_fence_after();
 #pragma unroll
             for (int c = 0; c < COLS / 2; c += 32) tmem_st_x32(p_addr + c, pr + c);
             if (__any_sync(0xffffffffu, need_rescale)) {
