@@ -58,6 +58,37 @@ def needs_build() -> bool:
         return f.read().strip() != _digest()
 
 
+def build_variant(lib_path: str, defines: list[str], sources: list[str] | None = None) -> str:
+    """A private copy of the library with extra -D switches (tuning / timing experiments: tools/attn_variants.py,
+    tools/gemm_dbg.sh). Never the product library: _native.load_library(path) loads it explicitly."""
+    nvcc = _nvcc()
+    obj_dir = lib_path + ".obj"
+    os.makedirs(obj_dir, exist_ok=True)
+    procs, objs = [], []
+    for src in _sources():
+        obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
+        objs.append(obj)
+        flags = [f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")]
+        extra = defines if (sources is None or src in sources) else []
+        base_obj = os.path.join(PKG_DIR, "build", src.replace(".cu", ".o"))
+        if not extra and os.path.exists(base_obj) and not needs_build():
+            objs[-1] = base_obj                                   # unchanged translation unit: reuse the product object
+            continue
+        procs.append((src, subprocess.Popen([nvcc, *flags, *extra, "-I", CSRC, "-c", os.path.join(CSRC, src), "-o", obj],
+                                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for src, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            sys.stderr.write(out)
+            raise RuntimeError(f"nvcc failed for variant {lib_path} ({src})")
+    r = subprocess.run([nvcc, "-shared", "-o", lib_path, *objs, "-lcudart"], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("link failed")
+    return lib_path
+
+
 def build(force: bool = False, verbose: bool = True) -> str:
     """Compile every .cu into objects (in parallel) and link the shared library."""
     if not force and not needs_build():

@@ -409,7 +409,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll 8
                 for (int i = 0; i < COLS; ++i)
                     if (i < n_valid)
-                        sr[i] = __float_as_uint(fmaf(__ldg(mrow + i), p.inv_scale, __uint_as_float(sr[i])));
+                        // (-inf entries are taken as -1e30, like boolean masks: a key tile whose entries are all
+                        // -inf would otherwise make the running max -inf and alpha = 2^(-inf + inf) a NaN)
+                        sr[i] = __float_as_uint(fmaf(fmaxf(__ldg(mrow + i), -1.0e30f), p.inv_scale, __uint_as_float(sr[i])));
             }
             if constexpr (RAGGED) {
 #pragma unroll

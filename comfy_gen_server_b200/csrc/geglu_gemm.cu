@@ -30,7 +30,9 @@
 // Tensor-core bound. Algorithmic FLOPs = 2 * M * K * (2N) for GEGLU, 2 * M * K * N for linear.
 #include "common.cuh"
 
-#include <stdlib.h>
+#ifndef CGS_GEMM_EXPT
+#define CGS_GEMM_EXPT 0
+#endif
 
 namespace cgs {
 
@@ -86,7 +88,10 @@ template <int EPI>
 __global__ void __launch_bounds__(gemm::THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
-            __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr, int dbg) {
+            __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr) {
+    // timing experiments with wrong results are compile-time only (-DCGS_GEMM_EXPT=<bits>, tools/gemm_dbg.sh builds a
+    // private copy of the library): 1 no GELU, 2 no stores, 4 reload A instead of B, 8 one MMA per k-block
+    constexpr int dbg = CGS_GEMM_EXPT;
     using namespace gemm;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -365,10 +370,6 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
         int rc = make_tmap_bf16(&tmO, out, 2, dims, strides, box);
         if (rc != kOk) return rc;
     }
-    static const int dbg = [] {                 // developer knob (tools/gemm_dbg.sh), read once per process
-        const char* e = getenv("CGS_GEMM_DEBUG");
-        return e ? atoi(e) : 0;
-    }();
     const int tiles_m = (int)((M + BM - 1) / BM);
     const int tiles_n = (epi == EPI_GEGLU) ? N / BN_HALF : (N + UMMA_N - 1) / UMMA_N;
     const long long tiles = (long long)tiles_m * tiles_n;
@@ -380,12 +381,12 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
         CGS_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<EPI_GEGLU>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         gemm_kernel<EPI_GEGLU><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K,
-                                                                      (int)ldo, (int)ldr, dbg);
+                                                                      (int)ldo, (int)ldr);
     } else {
         CGS_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<EPI_LINEAR>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         gemm_kernel<EPI_LINEAR><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K,
-                                                                       (int)ldo, (int)ldr, dbg);
+                                                                       (int)ldo, (int)ldr);
     }
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;

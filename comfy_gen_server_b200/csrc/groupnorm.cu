@@ -9,6 +9,8 @@
 // L2: one HBM read + one HBM write. Algorithmic bytes = 2 * N*C*H*W * 2.
 #include "common.cuh"
 
+#include <atomic>
+
 namespace cgs {
 
 // x * sigmoid(x) = h + h * tanh(h), h = x / 2: one MUFU (tanh.approx, rel. error ~2^-11, below the bf16 rounding of the
@@ -430,7 +432,9 @@ constexpr long long kGnStaticScratchBytes = 1 << 20;
 static __device__ __align__(256) float g_gn_static_scratch[kGnStaticScratchBytes / sizeof(float)];
 // In host code the name above is only a handle for the runtime, not a device address: the address each device
 // assigned to its copy has to be asked for, per device, and is cached here.
-static float* g_gn_static_scratch_addr[64] = {nullptr};
+// (atomic slots: two host threads may make a device's first call at the same time; both look the address up and
+// store the same value)
+static std::atomic<float*> g_gn_static_scratch_addr[64];
 }  // namespace cgs
 
 extern "C" int cgs_groupnorm_nhwc_noalloc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta,
@@ -452,16 +456,27 @@ extern "C" int cgs_groupnorm_nhwc_noalloc_fwd(const void* x, const void* add_nc,
             return kScratchTooSmall;
         }
     }
-    if (g_gn_static_scratch_addr[dev] == nullptr) {
+    // The scratch array used is the CURRENT device's copy: the tensors have to live there too, or the kernels
+    // would be handed a pointer into another GPU's memory.
+    if (x != nullptr) {
+        cudaPointerAttributes attr;
+        CGS_CUDA_CHECK(cudaPointerGetAttributes(&attr, x));
+        if (attr.type == cudaMemoryTypeDevice && attr.device != dev) {
+            set_last_error("groupnorm_nhwc_noalloc: x lives on device %d but device %d is current; make the tensors' "
+                           "device current before the call", attr.device, dev);
+            return kBadArgument;
+        }
+    }
+    float* scratch = g_gn_static_scratch_addr[dev].load(std::memory_order_acquire);
+    if (scratch == nullptr) {
         // once per device, with that device current (it is: cudaGetDevice above)
-        float* p = nullptr;
-        CGS_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_scratch));
-        if (p == nullptr) {
+        CGS_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_gn_static_scratch));
+        if (scratch == nullptr) {
             set_last_error("groupnorm_nhwc_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev);
             return kCudaError;
         }
-        g_gn_static_scratch_addr[dev] = p;
+        g_gn_static_scratch_addr[dev].store(scratch, std::memory_order_release);
     }
-    return cgs_groupnorm_nhwc_fwd(x, add_nc, gamma, beta, y, g_gn_static_scratch_addr[dev], kGnStaticScratchBytes, N, C,
-                                  HW, groups, eps, silu, stream);
+    return cgs_groupnorm_nhwc_fwd(x, add_nc, gamma, beta, y, scratch, kGnStaticScratchBytes, N, C, HW, groups, eps,
+                                  silu, stream);
 }

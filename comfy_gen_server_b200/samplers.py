@@ -494,13 +494,13 @@ class CFGGuider:
         if not self._fused_predicate(x, model_options):
             return None
         st = self._fused
+        if st is False:                 # this sample() call's conds are not plain: the generic composition runs
+            return None
         if st is None or st["batch"] != x.shape[0] or st["context"].device != x.device:
             st = self._fused = self._build_fused(x, model_options)
             if st is None:
                 self._fused = False
                 return None
-        if st is False:
-            return None
         m = self.inner_model
         ms = m.model_sampling
         tables = st["tables"]
@@ -622,11 +622,12 @@ class CFGGuider:
         identity of the weights (a LoRA patch or a reload replaces or rewrites parameter tensors)."""
         m = self.inner_model
         params = list(m.diffusion_model.parameters())
-        weights = tuple((p.data_ptr(), p._version) for p in params[::37])
+        weights = hash(tuple((p.data_ptr(), p._version) for p in params))      # every tensor: ~1.7 k pointers per call
         topt = model_options.get("transformer_options", {})
         return (tuple(x.shape), str(x.device), st["copies"], tuple(st["cond_or_uncond"]), float(self.cfg),
                 m.model_sampling.pred_type, float(m.model_sampling.sigma_data), tuple(st["context"].shape),
-                None if st["y"] is None else tuple(st["y"].shape), tuple(sorted(map(str, topt.keys()))),
+                None if st["y"] is None else tuple(st["y"].shape),
+                tuple(sorted((str(k), id(v)) for k, v in topt.items())),
                 len(params), weights,
                 # the code the capture recorded: feature switches and the op bindings (tools and tests rebind them)
                 tuple(sorted(_native.FEATURES.items())),

@@ -128,6 +128,8 @@ int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma,
  *     stream capture begins.
  *   - All calls on a device share the array; it is never cleared and need not be, but calls whose kernels overlap
  *     on the GPU (other streams, other threads) race on it -- serialise them.
+ *   - The tensors must live on the device that is current at the call (checked for x: CGS_BAD_ARGUMENT otherwise);
+ *     the address look-up is safe when several host threads make a device's first call at once.
  *   - Allocates and frees nothing.
  */
 int cgs_groupnorm_nhwc_noalloc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,

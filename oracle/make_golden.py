@@ -293,7 +293,7 @@ def gen_workflows():
     save("workflows_tiny_sd15", **out)
 
 
-def gen_sdxl_headline(seed=46, hw=128, steps=30, first_steps=2):
+def gen_sdxl_headline(seed=46, hw=128, steps=30, first_steps=2, name="e2e_sdxl_headline_2steps"):
     """The headline configuration at full size (BASELINE.json configs[2]: SDXL 1024^2, DPM++ 2M Karras, CFG 7; one
     image): the first `first_steps` steps of the 30-step schedule through the reference's fp32 CPU path
     (comfy.sample.sample with last_step), which pins the full-size network and the multistep update."""
@@ -311,12 +311,12 @@ def gen_sdxl_headline(seed=46, hw=128, steps=30, first_steps=2):
                                   last_step=first_steps, force_full_denoise=False)
     dt = time.time() - t0
     print(f"e2e_sdxl_headline: reference ran {first_steps} of {steps} steps in {dt:.1f}s; out std {out.std():.4f}")
-    save("e2e_sdxl_headline_2steps", x_after=out, noise=noise, positive=pos, negative=neg, pooled_pos=pp, pooled_neg=pn,
+    save(name, x_after=out, noise=noise, positive=pos, negative=neg, pooled_pos=pp, pooled_neg=pn,
          seed=np.int64(seed), steps=np.int64(steps), first_steps=np.int64(first_steps), ref_seconds=np.float64(dt),
          ref_threads=np.int64(torch.get_num_threads()))
 
 
-def gen_sd21v_full(seed=47, hw=96, steps=25, first_steps=3):
+def gen_sd21v_full(seed=47, hw=96, steps=25, first_steps=3, name="e2e_sd21v_full_3steps"):
     """BASELINE.json configs[3] at full size (SD2.1-v 768^2, Euler / normal, CFG 7, v-prediction; one image): the first
     steps through the reference's fp32 CPU path. Token counts 9216 / 2304 / 576 / 144 are not multiples of 128."""
     fam = uc.FAMILIES["sd21v"]
@@ -331,7 +331,7 @@ def gen_sd21v_full(seed=47, hw=96, steps=25, first_steps=3):
                                   seed=seed, disable_pbar=True, last_step=first_steps, force_full_denoise=False)
     dt = time.time() - t0
     print(f"e2e_sd21v_full: reference ran {first_steps} of {steps} steps in {dt:.1f}s; out std {out.std():.4f}")
-    save("e2e_sd21v_full_3steps", x_after=out, noise=noise, positive=pos, negative=neg, seed=np.int64(seed),
+    save(name, x_after=out, noise=noise, positive=pos, negative=neg, seed=np.int64(seed),
          steps=np.int64(steps), first_steps=np.int64(first_steps), ref_seconds=np.float64(dt),
          ref_threads=np.int64(torch.get_num_threads()))
 
@@ -346,6 +346,12 @@ def main():
         return
     if "--only-workflows" in sys.argv:
         gen_workflows()
+        return
+    if "--only-full-schedules" in sys.argv:
+        # north_star's bar is the cosine of the FINAL latents after the whole schedule: the headline configuration
+        # (30 DPM++ 2M steps, ~20 min on 8 cores) and config 4 (25 Euler steps, v-prediction) at full size
+        gen_sd21v_full(first_steps=25, name="e2e_sd21v_full_schedule")
+        gen_sdxl_headline(first_steps=30, name="e2e_sdxl_headline_full_schedule")
         return
     gen_attention()
     if "--only-attention" in sys.argv:

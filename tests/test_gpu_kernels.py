@@ -72,6 +72,21 @@ def test_masked_attention_large_and_fully_masked_rows():
     assert torch.isfinite(out).all() and (out - ref).abs().max() < ATTN_TOL
 
 
+def test_masked_attention_minus_inf_float_mask_first_tile_fully_masked():
+    """An additive float mask with -inf entries (what SDPA callers pass): rows whose first 128-key tile is entirely
+    -inf while later tiles hold valid keys must come out finite and equal to the reference on the valid keys."""
+    n = N()
+    B, H, Nq, Nk, d = 1, 2, 200, 400, 64
+    q, k, v = bf(randn((B, Nq, H * d), 1)), bf(randn((B, Nk, H * d), 2)), bf(randn((B, Nk, H * d), 3))
+    mask = torch.zeros((B, 1, Nq, Nk))
+    mask[:, :, 10:60, :128] = float("-inf")          # first key tile fully masked for 50 rows
+    mask[:, :, 100:120, :300] = float("-inf")        # first two tiles and part of the third
+    out = n.attention(q, k, v, H, mask.cuda()).float().cpu()
+    ref = O.attention(q.float().cpu(), k.float().cpu(), v.float().cpu(), H, mask)
+    assert torch.isfinite(out).all()
+    assert (out - ref).abs().max() < ATTN_TOL
+
+
 ATTN_SHAPES = [
     # B, H, Nq, Nk, d          -- the geometries of SURVEY.md section 8 (scaled-down batch)
     (2, 10, 4096, 4096, 64), (1, 20, 1024, 1024, 64), (2, 10, 4096, 77, 64), (2, 20, 1024, 154, 64),
@@ -79,6 +94,9 @@ ATTN_SHAPES = [
     (2, 8, 64, 77, 160), (1, 5, 9216, 9216, 64), (2, 10, 2304, 2304, 64), (2, 20, 576, 576, 64),
     (2, 20, 144, 144, 64), (2, 20, 144, 77, 64), (1, 1, 1, 1, 64), (3, 2, 129, 255, 64), (1, 2, 300, 231, 8),
     (1, 3, 257, 16, 16),
+    # instantiations the first round never ran: <2,2,2,128> (64 < d <= 128 with more than 8 key tiles: SD1.5 above
+    # 512^2), <3,1,1> (d = 160) with many key tiles and ragged ends
+    (1, 8, 2304, 2304, 80), (1, 4, 1500, 3000, 128), (1, 8, 1300, 1300, 160), (1, 2, 700, 2100, 96),
 ]
 
 
@@ -90,6 +108,25 @@ def test_attention_vs_fp32(B, H, Nq, Nk, d):
     ref = (torch.softmax(qf @ kf.transpose(-1, -2) * d ** -0.5, -1) @ vf).transpose(1, 2).reshape(B, Nq, H * d)
     assert not torch.isnan(out).any()
     assert (out - ref).abs().max() < ATTN_TOL
+
+
+def test_attention_config5_16384_tokens_vs_fp32_rows():
+    """BASELINE.json configs[4]: the 16384-token self-attention of SDXL 2048^2 (10 heads, d 64), compared with the
+    fp32 computation on a subset of query rows (all keys): first / last tiles, tile borders, and a random sample."""
+    B, H, Nn, d = 1, 10, 16384, 64
+    q, k, v = bf(randn((B, Nn, H * d), 1)), bf(randn((B, Nn, H * d), 2)), bf(randn((B, Nn, H * d), 3))
+    out = N().attention(q, k, v, H).float()
+    rows = torch.cat([torch.arange(0, 130), torch.arange(383, 387), torch.arange(8190, 8194),
+                      torch.arange(Nn - 130, Nn),
+                      torch.randint(0, Nn, (256,), generator=torch.Generator().manual_seed(5))]).unique().cuda()
+    qf = q.float().view(B, Nn, H, d)[:, rows].transpose(1, 2)                   # [B, H, R, d]
+    kf, vf = (t.float().view(B, Nn, H, d).transpose(1, 2) for t in (k, v))
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * d ** -0.5, -1) @ vf).transpose(1, 2).reshape(B, len(rows), H * d)
+    assert torch.isfinite(out).all()
+    assert (out[:, rows] - ref).abs().max() < ATTN_TOL
+    # size-independent property on the whole output: constant values -> constant output (softmax rows sum to one)
+    half = torch.full_like(v, 0.5)
+    assert (N().attention(q, k, half, H).float() - 0.5).abs().max() < 4e-3
 
 
 def test_attention_large_logits_rescale_path():

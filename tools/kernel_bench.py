@@ -16,6 +16,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from comfy_gen_server_b200 import _native as N  # noqa: E402
 
+if os.environ.get("CGS_LIB"):          # a private variant build (tools/gemm_dbg.sh, tools/attn_variants.py)
+    N._lib = N.load_library(os.path.join(ROOT, os.environ["CGS_LIB"]))
+
 PEAKS = {"hbm_gbs": 6554.6, "bf16_tflops": 1650.7}
 try:
     with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
