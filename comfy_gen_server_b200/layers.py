@@ -1,0 +1,136 @@
+"""Operator-level entry points of the B200 path, written as functions over the reference's OWN module classes
+(comfy/ops.py, comfy/ldm/modules/attention.py): integration.install() binds them as the `forward` of those classes
+and as the module-level attention function. They never subclass or re-declare a reference class.
+
+Routing rule, the same everywhere: a bf16 CUDA tensor runs the hand-written kernel (through the C ABI,
+_native.py); anything else -- the CLIP text encoder on the CPU, an fp32 VAE, a manual-cast module -- is handed to the
+function that was bound before install(), i.e. stays exactly what the reference does. The attention function is the
+exception: `optimized_attention` is the UNet's hot call and has no other implementation here, so it raises for
+tensors the kernel cannot take (the reference's CPU / small-input callers go through
+optimized_attention_for_device, attention.py:370-383, which install() leaves alone).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _native
+
+# the functions that were bound before install() (filled in by integration.install)
+ORIGINAL: dict = {}
+
+
+# What the kernels take. (Module attributes rather than literals so that the CPU test-suite can run this host code
+# against a torch stand-in for _native: tests/fake_native.py. Nothing in the product changes them.)
+ACT_DTYPE = torch.bfloat16
+DEVICE_TYPE = "cuda"
+
+
+def on_fast_device(t: torch.Tensor) -> bool:
+    """A tensor of the UNet's activation type on the device the kernels run on."""
+    return t.device.type == DEVICE_TYPE and t.dtype == ACT_DTYPE
+
+
+def is_latent(t: torch.Tensor) -> bool:
+    """A sampler-side tensor the tail kernels take: contiguous fp32 on the device."""
+    return t.device.type == DEVICE_TYPE and t.dtype == torch.float32 and t.is_contiguous()
+
+
+def _cast(module, x):
+    """weight / bias of a reference op module for input x: the reference's per-call cast (comfy/ops.py:22-32) when
+    the module asks for it (manual_cast classes, low-vram weight functions), the parameters themselves otherwise."""
+    if module.comfy_cast_weights:
+        import comfy.ops
+        return comfy.ops.cast_bias_weight(module, x)
+    return module.weight, module.bias
+
+
+# ----------------------------------------------------------------------------------------------
+# attention  (comfy/ldm/modules/attention.py:337-368)
+# ----------------------------------------------------------------------------------------------
+def attention_b200(q, k, v, heads, mask=None):
+    """Drop-in for attention_pytorch: q [B, Nq, heads*d], k/v [B, Nk, heads*d] -> [B, Nq, heads*d]; inputs are not
+    modified. cgs_attention_fwd, or cgs_attention_masked_fwd when a mask is given (boolean keep-mask or additive
+    float, attention.py:111-123). No SDPA, no fallback."""
+    if not on_fast_device(q):
+        raise RuntimeError(f"attention_b200: bf16 CUDA tensors required, got {q.dtype} on {q.device} "
+                           "(run the UNet in bf16: install() sets --bf16-unet; CPU callers use "
+                           "optimized_attention_for_device)")
+    return _native.attention(q, k, v, heads, mask)
+
+
+# ----------------------------------------------------------------------------------------------
+# ops.LayerNorm / ops.GroupNorm  (comfy/ops.py:82-113)
+# ----------------------------------------------------------------------------------------------
+def layernorm_forward(self, input):
+    if on_fast_device(input) and self.weight is not None and self.bias is not None and len(self.normalized_shape) == 1:
+        weight, bias = _cast(self, input)
+        if weight.dtype == ACT_DTYPE:
+            return _native.layer_norm(input, weight, bias, self.eps)
+    return ORIGINAL["LayerNorm.forward"](self, input)
+
+
+def groupnorm_kernel_ok(self, input) -> bool:
+    if not (on_fast_device(input) and input.dim() == 4 and self.affine):
+        return False
+    c = input.shape[1]
+    if input.is_contiguous():                                       # NCHW kernel
+        return (input.shape[2] * input.shape[3]) % 8 == 0
+    if input.is_contiguous(memory_format=torch.channels_last):      # NHWC kernels
+        return c % 8 == 0 and c // self.num_groups >= 8 and self.num_groups <= 32 and c <= 2560
+    return False
+
+
+def groupnorm_apply(self, input, silu: bool = False, add_nc: Optional[torch.Tensor] = None):
+    """GroupNorm with the SiLU that follows it in a ResBlock and the per-(sample, channel) addend that precedes it
+    (timestep embedding + the previous convolution's bias) in one kernel; the reference's three library calls
+    when the tensor is not one the kernels take."""
+    weight, bias = _cast(self, input)
+    if groupnorm_kernel_ok(self, input) and weight.dtype == ACT_DTYPE:
+        return _native.group_norm(input, weight, bias, self.num_groups, self.eps, silu, add_nc)
+    if add_nc is not None:
+        input = input + add_nc[..., None, None]
+    out = torch.nn.functional.group_norm(input, self.num_groups, weight, bias, self.eps)
+    return torch.nn.functional.silu(out) if silu else out
+
+
+def groupnorm_forward(self, input):
+    if groupnorm_kernel_ok(self, input):
+        return groupnorm_apply(self, input)
+    return ORIGINAL["GroupNorm.forward"](self, input)
+
+
+# ----------------------------------------------------------------------------------------------
+# GEGLU  (comfy/ldm/modules/attention.py:56-63)
+# ----------------------------------------------------------------------------------------------
+def geglu_forward(self, x):
+    """Linear -> chunk -> gelu -> mul as ONE GEMM with the gate in its epilogue; the [M, 2N] tensor never exists."""
+    proj = self.proj
+    if on_fast_device(x) and proj.weight.shape[0] % 256 == 0 and proj.weight.shape[1] % 8 == 0:
+        weight, bias = _cast(proj, x)
+        if weight.dtype == ACT_DTYPE:
+            return _native.geglu(x, weight, bias)
+    return ORIGINAL["GEGLU.forward"](self, x)
+
+
+# ----------------------------------------------------------------------------------------------
+# convolutions
+# ----------------------------------------------------------------------------------------------
+def conv_plain(conv) -> bool:
+    """A resident bf16 Conv2d whose bias may be applied by the consumer of its output."""
+    return (isinstance(conv, torch.nn.Conv2d) and not conv.comfy_cast_weights and conv.weight_function is None
+            and conv.bias_function is None and conv.bias is not None and conv.bias.dtype == ACT_DTYPE
+            and conv.weight.dtype == ACT_DTYPE)
+
+
+def conv_nobias(conv, x):
+    """The convolution without its bias: ATen adds a cuDNN convolution's bias in a separate full pass over the
+    output, so the caller hands the bias to the kernel that consumes this output (GroupNorm's addend, the residual
+    add, the skip concatenation)."""
+    return conv._conv_forward(x, conv.weight, None)
+
+
+def linear_plain(lin) -> bool:
+    return (not lin.comfy_cast_weights and lin.weight_function is None and lin.bias_function is None
+            and lin.weight.dtype == ACT_DTYPE)

@@ -42,3 +42,22 @@ def randn(shape, seed, scale=1.0):
 def cosine(a, b):
     a, b = a.detach().double().flatten(), b.detach().double().flatten()
     return float((a @ b) / (a.norm() * b.norm()))
+
+
+@pytest.fixture(scope="session")
+def reference_tree():
+    """`import comfy` works (the staged copy under baseline/_ref on the GPU box; --cpu mode on machines without a GPU)."""
+    from comfy_gen_server_b200.reference import ensure_importable
+    where = ensure_importable(cpu=not torch.cuda.is_available())
+    import comfy.utils
+    comfy.utils.PROGRESS_BAR_ENABLED = False
+    return where
+
+
+@pytest.fixture
+def installed(reference_tree):
+    """integration.install() for the duration of a test (undone afterwards)."""
+    from comfy_gen_server_b200 import integration
+    integration.install()
+    yield
+    integration.uninstall()

@@ -1,6 +1,8 @@
 """CPU-only checks of the host side: the C-ABI library loads and exports every symbol declared in
-include/cgs_b200.h, schedules / coefficients are bit-identical to the reference's (golden), cond
-batching, placement logic, and the 2-rank gloo paths of the multi-GPU plumbing. No compute kernels run."""
+include/cgs_b200.h; the product refuses CPU tensors and never touches the oracle; install() rebinds the reference
+tree and uninstall() restores it; and -- with tests/fake_native.py standing in for the kernels -- the whole drop-in
+(comfy.sample.sample with install() active) reproduces the reference's golden latents, falls through to the
+reference's composition for hooks / non-plain conds, and shards across two gloo ranks. No compute kernels run."""
 import os
 import re
 import sys
@@ -10,7 +12,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from conftest import ROOT, load_golden, randn
+from conftest import ROOT, load_golden, randn, cosine
 
 
 def test_cabi_library_exports_every_declared_symbol():
@@ -25,16 +27,18 @@ def test_cabi_library_exports_every_declared_symbol():
 
 
 def test_product_refuses_cpu_tensors():
-    from comfy_gen_server_b200 import _native, attention as A, ops
+    from comfy_gen_server_b200 import _native, layers
     q = torch.zeros(1, 8, 64, dtype=torch.bfloat16)
     with pytest.raises(RuntimeError):
         _native.attention(q, q, q, 1)
     with pytest.raises(RuntimeError):
-        A.optimized_attention(q, q, q, 1)
+        layers.attention_b200(q, q, q, 1)
     with pytest.raises(RuntimeError):
-        ops.b200_ops.LayerNorm(64, dtype=torch.bfloat16)(q)
+        _native.layer_norm(q, q[0, 0], q[0, 0])
     with pytest.raises(RuntimeError):
-        A.optimized_attention_for_device(torch.device("cpu"))
+        _native.geglu(q, torch.zeros(128, 64, dtype=torch.bfloat16), None)
+    with pytest.raises(RuntimeError):
+        _native.cfg_denoise(torch.zeros(1, 4, 8, 8), None, torch.zeros(1, 4, 8, 8), torch.ones(1), 1.0, 0)
     with pytest.raises(_native.NativeLibraryError):
         _native.load_library("/nonexistent/libcgs_b200.so")
 
@@ -48,25 +52,21 @@ def test_product_never_imports_the_oracle():
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
 
 
-def test_schedules_bit_identical_to_reference():
-    from comfy_gen_server_b200 import samplers as S
-    from comfy_gen_server_b200.model_sampling import model_sampling
-    g = load_golden("schedules")
-    ms = model_sampling("eps")
-    assert torch.equal(ms.sigmas, g["sigmas_table"])
-    for key in ("karras_30", "normal_20", "simple_20", "sgm_uniform_20", "karras_7", "normal_25"):
-        sched, steps = key.rsplit("_", 1)
-        assert torch.equal(S.calculate_sigmas(ms, sched, int(steps)), g[key]), key
-    assert torch.equal(ms.timestep(g["karras_30"][:-1]), g["timestep_karras_30"])
-    mv = model_sampling("v")
-    assert torch.equal(mv.calculate_denoised(g["ci.sigma"], g["ci.model_out"], g["ci.x"]), g["denoised_v"])
-    assert torch.equal(ms.calculate_denoised(g["ci.sigma"], g["ci.model_out"], g["ci.x"]), g["denoised_eps"])
-    assert torch.equal(ms.calculate_input(g["ci.sigma"], g["ci.x"]), g["calculate_input"])
+def test_product_declares_no_copy_of_a_reference_class():
+    """The host side is a plug-in: it binds functions onto the reference's classes and must not re-declare them."""
+    pkg = os.path.join(ROOT, "comfy_gen_server_b200")
+    forbidden = ("CrossAttention", "BasicTransformerBlock", "SpatialTransformer", "UNetModel", "ResBlock", "KSampler",
+                 "KSAMPLER", "ModelPatcher", "BaseModel", "ModelSamplingDiscrete", "CONDRegular", "CONDCrossAttn")
+    for f in os.listdir(pkg):
+        if f.endswith(".py"):
+            src = open(os.path.join(pkg, f)).read()
+            for name in forbidden:
+                assert not re.search(rf"^class\s+{name}\b", src, re.M), (f, name)
 
 
 def test_dpmpp2m_coefficients_reproduce_reference_update():
     """x' = c_x x - c_d (c_cur D - c_old D_old) with host coefficients == the reference loop, bit for bit."""
-    from comfy_gen_server_b200.k_diffusion import sampling as ks
+    from comfy_gen_server_b200 import sampling as ks
     g = load_golden("sampler_kat")
     key = "dpmpp_2m_karras_30"
     sig = g[key + ".sigmas"]
@@ -82,61 +82,8 @@ def test_dpmpp2m_coefficients_reproduce_reference_update():
     assert torch.equal(x, g[key + ".final"])
 
 
-def test_cond_batching_order_and_lcm_padding():
-    from comfy_gen_server_b200 import samplers as S
-    from comfy_gen_server_b200.conds import CONDCrossAttn
-    g = load_golden("cfg")
-
-    class Stub:
-        def __init__(self):
-            self.calls = []
-
-        def memory_required(self, shape):
-            return 0
-
-        def apply_model(self, x, t, c_crossattn=None, transformer_options=None, **kw):
-            self.calls.append((tuple(c_crossattn.shape), list(transformer_options["cond_or_uncond"])))
-            return x * 0.5 + c_crossattn.mean(dim=(1, 2)).view(-1, 1, 1, 1) + t.view(-1, 1, 1, 1) * 0.01
-    mk = lambda c: [{"model_conds": {"c_crossattn": CONDCrossAttn(c)}}]
-    stub = Stub()
-    out = S.sampling_function(stub, g["x"], g["sigma"], mk(g["uncond"]), mk(g["cond"]), 7.0, model_options={})
-    assert stub.calls == [((4, 154, 32), [1, 0])]
-    assert torch.equal(out, g["out_cfg7"])
-    stub1 = Stub()
-    out1 = S.sampling_function(stub1, g["x"], g["sigma"], mk(g["uncond"]), mk(g["cond"]), 1.0, model_options={})
-    assert stub1.calls[0][1] == [0] and torch.equal(out1, g["out_cfg1"])
-    assert torch.equal(S.cfg_function(None, g["cond_pred"], g["uncond_pred"], 7.0, g["x"], g["sigma"]),
-                       g["cfg_function"])
-
-
-def test_cfg_hooks_and_timestep_ranges():
-    from comfy_gen_server_b200 import samplers as S
-    from comfy_gen_server_b200.conds import CONDCrossAttn
-    x, sigma = randn((2, 4, 8, 8), 1), torch.tensor([2.5, 2.5])
-
-    class Stub:
-        def memory_required(self, shape):
-            return 0
-
-        def apply_model(self, x, t, c_crossattn=None, transformer_options=None, **kw):
-            return x * 0.5 + c_crossattn.mean(dim=(1, 2)).view(-1, 1, 1, 1)
-    mk = lambda c, **kw: [dict({"model_conds": {"c_crossattn": CONDCrossAttn(c)}}, **kw)]
-    cp, cn = randn((1, 77, 16), 2), randn((1, 77, 16), 3)
-    base = S.sampling_function(Stub(), x, sigma, mk(cn), mk(cp), 3.0, model_options={})
-    seen = []
-    opts = {"sampler_cfg_function": lambda a: (seen.append(sorted(a.keys())),
-                                               a["uncond"] + (a["cond"] - a["uncond"]) * a["cond_scale"])[1],
-            "sampler_post_cfg_function": [lambda a: a["denoised"] + 1.0]}
-    hooked = S.sampling_function(Stub(), x, sigma, mk(cn), mk(cp), 3.0, model_options=opts)
-    assert (hooked - (base + 1.0)).abs().max() < 1e-5
-    assert "cond_denoised" in seen[0] and "input" in seen[0]
-    # a cond outside its timestep range is skipped: the output for that side is zeros / 1e-37 -> 0
-    skipped = S.calc_cond_batch(Stub(), [mk(cp, timestep_start=1.0), mk(cn)], x, sigma, {})
-    assert skipped[0].abs().max() == 0 and skipped[1].abs().max() > 0
-
-
 def test_placement_plans():
-    from comfy_gen_server_b200 import model_management as mm
+    from comfy_gen_server_b200 import placement as mm
     # config 3: SDXL batch 8 on 1/2/4/8 GPUs -> pure batch sharding
     for world in (1, 2, 4, 8):
         ps = [mm.plan_placement(8, world, r) for r in range(world)]
@@ -154,11 +101,139 @@ def test_placement_plans():
         mm.plan_placement(4, 3, 0, cfg_split=True)
 
 
+# ----------------------------------------------------------------------------------------------
+# the drop-in, end to end, with torch stand-ins for the kernels
+# ----------------------------------------------------------------------------------------------
+def test_install_rebinds_the_reference_tree_and_uninstall_restores_it(reference_tree):
+    import comfy.cli_args
+    import comfy.k_diffusion.sampling as rk
+    import comfy.ldm.modules.attention as ra
+    import comfy.ldm.modules.diffusionmodules.openaimodel as ru
+    import comfy.model_base as rb
+    import comfy.model_management as rm
+    import comfy.ops as ro
+    import comfy.samplers as rs
+    from comfy_gen_server_b200 import integration as b200, layers
+    targets = lambda: (ra.optimized_attention, ra.optimized_attention_masked, ra.GEGLU.forward,
+                       ro.disable_weight_init.LayerNorm.forward, ro.disable_weight_init.GroupNorm.forward,
+                       ra.BasicTransformerBlock._forward, ra.SpatialTransformer.forward, ru.ResBlock._forward,
+                       ru.Upsample.forward, ru.UNetModel.forward, rb.BaseModel.apply_model, rk.sample_euler,
+                       rk.sample_dpmpp_2m, comfy.cli_args.args.bf16_unet, hasattr(rm, "plan_placement"))
+    orig = targets()
+    log = b200.install()
+    try:
+        assert b200.installed() and len(log) >= 14
+        assert ra.optimized_attention is layers.attention_b200 and ra.optimized_attention_masked is layers.attention_b200
+        assert all(a is not b for a, b in zip(orig[:13], targets()[:13]))
+        assert comfy.cli_args.args.bf16_unet is True and rm.plan_placement(8, 2, 1).start == 4
+        assert rs.ksampler("dpmpp_2m").sampler_function is rk.sample_dpmpp_2m    # getattr lookup sees the new function
+        assert rs.ksampler("euler").sampler_function.__module__ == "comfy_gen_server_b200.sampling"
+        # manual_cast's classes inherit the rebound methods; the CPU-capable selector is untouched
+        assert ro.manual_cast.LayerNorm.forward is ro.disable_weight_init.LayerNorm.forward
+        assert ra.optimized_attention_for_device(torch.device("cpu")) is ra.attention_sub_quad
+        assert b200.install() == []                                               # idempotent
+    finally:
+        b200.uninstall()
+    assert targets() == orig and not b200.installed() and not layers.ORIGINAL
+
+
+def test_installed_ops_leave_other_callers_alone(reference_tree, installed):
+    """With install() active a CPU / fp32 caller of the reference's op classes (the text encoder, the VAE) still gets
+    the reference's own computation."""
+    import comfy.ops
+    ln = comfy.ops.disable_weight_init.LayerNorm(32)
+    gn = comfy.ops.manual_cast.GroupNorm(4, 32)
+    with torch.no_grad():
+        for p in list(ln.parameters()) + list(gn.parameters()):
+            p.copy_(randn(tuple(p.shape), 3) * 0.1 + 1.0)
+    x = randn((2, 5, 32), 1)
+    assert torch.equal(ln(x), torch.nn.functional.layer_norm(x, (32,), ln.weight, ln.bias, ln.eps))
+    img = randn((2, 32, 4, 4), 2)
+    assert torch.allclose(gn(img), torch.nn.functional.group_norm(img, 4, gn.weight, gn.bias, gn.eps))
+
+
+E2E = [("tiny_sdxl", "e2e_tiny_sdxl_dpmpp2m", 16, 30, "dpmpp_2m", "karras"),
+       ("tiny_sd15", "e2e_tiny_sd15_euler", 16, 20, "euler", "normal"),
+       ("tiny_sd21v", "e2e_tiny_sd21v_euler", 12, 25, "euler", "normal")]
+
+
+def _cpu_case(family, golden, hw):
+    import comfy.sample
+    from comfy_gen_server_b200 import models
+    g = load_golden(golden)
+    seed = int(g["seed"])
+    patcher, model = models.build_model(family, "cpu", seed=seed, dtype=torch.float32)
+    patcher.model_options["cuda_graph"] = False
+    latent = torch.zeros(2, 4, hw, hw)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    extra = lambda k: {"pooled_output": g[k]} if k in g else {}
+    return g, seed, patcher, latent, noise, [[g["positive"], extra("pooled_pos")]], [[g["negative"], extra("pooled_neg")]]
+
+
+@pytest.mark.parametrize("family,golden,hw,steps,sampler,sched", E2E)
+def test_drop_in_reproduces_reference_latents_with_torch_stand_ins(reference_tree, family, golden, hw, steps, sampler,
+                                                                   sched):
+    """comfy.sample.sample with install() active -- fused blocks, NHWC-capable UNet path, fused CFG + sampler step --
+    on fp32 CPU tensors with torch stand-ins for the kernels: equal to the reference's golden latents to fp32
+    rounding, i.e. the host-side plumbing (cond order, K/V caching, bias folding, coefficients) changes no result."""
+    import comfy.sample
+    import fake_native
+    from comfy_gen_server_b200 import integration
+    g, seed, patcher, latent, noise, pos, neg = _cpu_case(family, golden, hw)
+    with fake_native.patched() as calls, torch.inference_mode():
+        integration.install()
+        try:
+            out = comfy.sample.sample(patcher, noise, steps, 7.0, sampler, sched, pos, neg, latent, seed=seed,
+                                      disable_pbar=True)
+        finally:
+            integration.uninstall()
+    assert calls["cfg_sampler_tail"] == steps and calls["add_layer_norm_"] > 0 and calls["geglu"] > 0
+    assert (out - g["final"]).abs().max() < 2e-3 and cosine(out, g["final"]) > 0.999999
+
+
+def test_hooks_and_non_plain_conds_fall_through_to_the_reference_composition(reference_tree):
+    """(i) a post-CFG hook, (ii) an attention output patch, (iii) two positive conds with an area and a strength: the
+    fused step / fused block must stand aside for EVERY step and the result must equal the unmodified reference's."""
+    import comfy.sample
+    import fake_native
+    from comfy_gen_server_b200 import integration
+    g, seed, patcher, latent, noise, pos, neg = _cpu_case("tiny_sd15", "e2e_tiny_sd15_euler", 16)
+    steps = 3
+    run = lambda p, po=pos: comfy.sample.sample(p, noise, steps, 7.0, "euler", "normal", po, neg, latent, seed=seed,
+                                                disable_pbar=True)
+    hooked = patcher.clone()
+    post_calls = []
+    hooked.set_model_sampler_post_cfg_function(lambda a: (post_calls.append(1), a["denoised"] * 0.98)[1])
+    patched_attn = patcher.clone()
+    attn_calls = []
+    patched_attn.set_model_attn1_output_patch(lambda n, extra: (attn_calls.append(extra["block"]), n * 1.01)[1])
+    area_pos = [pos[0], [randn(tuple(g["positive"].shape), 77), {"area": (8, 16, 4, 0), "strength": 0.7}]]
+    with torch.inference_mode():
+        want = [run(hooked), run(patched_attn), run(patcher, area_pos)]
+        n_post, n_attn = len(post_calls), len(attn_calls)
+        with fake_native.patched() as calls:
+            integration.install()
+            try:
+                got = [run(hooked), run(patched_attn), run(patcher, area_pos)]
+                tails = calls.get("cfg_sampler_tail", 0)
+            finally:
+                integration.uninstall()
+    assert len(post_calls) == 2 * n_post == 2 * steps and len(attn_calls) == 2 * n_attn
+    # (ii) keeps the fused CFG + update step (the patch lives inside the UNet); (i) and (iii) must not use it
+    assert tails == steps
+    for a, b in zip(got, want):
+        assert (a - b).abs().max() < 2e-3, float((a - b).abs().max())
+
+
+# ----------------------------------------------------------------------------------------------
+# two gloo ranks
+# ----------------------------------------------------------------------------------------------
 def _dist_worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     sys.path.insert(0, ROOT)
-    from comfy_gen_server_b200 import model_management as mm
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from comfy_gen_server_b200 import placement as mm
     try:
         full_noise = torch.arange(5 * 4 * 2 * 2, dtype=torch.float32).view(5, 4, 2, 2)
         latent = torch.zeros_like(full_noise)
@@ -184,7 +259,38 @@ def _dist_worker(rank, world, port, q):
             u, c = -x + step, x + step
             x = u + (c - u) * 7.0
         ok2 = torch.equal(out2, x)
-        q.put((rank, ok1, ok2))
+
+        # the real thing on two ranks: sample_distributed through the reference's guider + install(), batch-sharded
+        # and CFG-split, against the 1-process comfy.sample.sample (torch stand-ins for the kernels)
+        from comfy_gen_server_b200.reference import ensure_importable
+        ensure_importable(cpu=True)
+        import comfy.sample
+        import comfy.utils
+        import fake_native
+        from comfy_gen_server_b200 import integration, models
+        comfy.utils.PROGRESS_BAR_ENABLED = False
+        torch.set_num_threads(2)
+        seed = 44
+        patcher, _ = models.build_model("tiny_sdxl", "cpu", seed=seed, dtype=torch.float32)
+        patcher.model_options["cuda_graph"] = False
+        g = lambda shape, s: torch.randn(shape, generator=torch.Generator().manual_seed(s))
+        lat = torch.zeros(3, 4, 16, 16)
+        noise = comfy.sample.prepare_noise(lat, seed)
+        pos = [[g((1, 77, 128), 1), {"pooled_output": g((1, 1280), 3)}]]
+        neg = [[g((1, 154, 128), 2), {"pooled_output": g((1, 1280), 4)}]]
+        with fake_native.patched(), torch.inference_mode():
+            integration.install()
+            ref = comfy.sample.sample(patcher, noise, 3, 7.0, "dpmpp_2m", "karras", pos, neg, lat, seed=seed,
+                                      disable_pbar=True)
+            a = mm.sample_distributed(patcher, noise, 3, 7.0, "dpmpp_2m", "karras", pos, neg, lat, seed=seed)
+            b = mm.sample_distributed(patcher, noise, 3, 7.0, "dpmpp_2m", "karras", pos, neg, lat, seed=seed,
+                                      cfg_split=True)
+            integration.uninstall()
+        # (a rank with ONE image takes other BLAS kernels than the batched run: fp32 rounding, amplified by CFG 7)
+        tol = 1e-3 * float(ref.abs().max())
+        ok3 = float((a - ref).abs().max()) < tol and a.shape == ref.shape
+        ok4 = float((b - ref).abs().max()) < tol and b.shape == ref.shape
+        q.put((rank, ok1, ok2, ok3, ok4))
     finally:
         dist.destroy_process_group()
 
@@ -196,66 +302,16 @@ def test_two_rank_gloo_sharding_gather_and_cfg_exchange():
     procs = [ctx.Process(target=_dist_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    res = sorted(q.get(timeout=120) for _ in range(2))
+    res = sorted(q.get(timeout=600) for _ in range(2))
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert res == [(0, True, True), (1, True, True)]
+    assert res == [(0, True, True, True, True), (1, True, True, True, True)]
 
 
-def test_unet_layout_matches_reference_key_names():
-    """State-dict keys / shapes of the product UNet equal unet_config.param_shapes, which oracle/make_golden.py
-    asserts equal to the reference UNetModel's state dict for every family."""
-    from comfy_gen_server_b200.model_base import build_model
+def test_reference_param_shapes_match_unet_config(reference_tree):
+    """unet_config.param_shapes (the seeded-weight layout shared by the oracle, the goldens and the GPU tests) equals
+    the state dict of the reference's UNetModel for the tiny families (models.build_model asserts it for any family)."""
+    from comfy_gen_server_b200 import models
     for fam in ("tiny_sd15", "tiny_sd21v", "tiny_sdxl"):
-        m = build_model(fam, device="cpu", seed=1)
-        own = {k: tuple(v.shape) for k, v in m.diffusion_model.state_dict().items()}
-        assert own == uc_shapes(fam)
-
-
-def uc_shapes(fam):
-    from comfy_gen_server_b200 import unet_config as uc
-    return uc.param_shapes(uc.FAMILIES[fam]["unet"])
-
-
-def test_install_into_reference_tree_rebinds_and_restores():
-    """Drop-in check against the real reference (only where /root/reference exists, i.e. the build container)."""
-    ref = os.environ.get("CGS_REFERENCE", "/root/reference")
-    if not os.path.isdir(os.path.join(ref, "comfy")):
-        pytest.skip("reference tree not present on this machine")
-    code = r'''
-import sys, types
-sys.path.insert(0, %r); sys.path.insert(0, %r)
-sys.modules["torchsde"] = types.ModuleType("torchsde")
-import comfy.cli_args; comfy.cli_args.args.cpu = True
-import comfy.ldm.modules.attention as ra, comfy.k_diffusion.sampling as rk, comfy.ops as ro
-import comfy_gen_server_b200.integration as b200
-orig = (ra.optimized_attention, rk.sample_euler, ro.disable_weight_init.LayerNorm.forward, ra.GEGLU.forward)
-log = b200.install()
-from comfy_gen_server_b200.attention import attention_b200
-assert ra.optimized_attention is attention_b200 and ra.optimized_attention_masked is attention_b200
-assert rk.sample_dpmpp_2m.__module__.startswith("comfy_gen_server_b200") and len(log) >= 9
-import comfy.samplers as rs
-assert rs.ksampler("dpmpp_2m").sampler_function is rk.sample_dpmpp_2m      # getattr lookup sees the new function
-b200.uninstall()
-assert (ra.optimized_attention, rk.sample_euler, ro.disable_weight_init.LayerNorm.forward, ra.GEGLU.forward) == orig
-print("OK")
-''' % (ref, ROOT)
-    import subprocess
-    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
-    assert p.returncode == 0 and "OK" in p.stdout, p.stdout[-1500:] + p.stderr[-1500:]
-
-
-def test_sampler_nodes_surface():
-    """nodes.py:1441-1465, 1753-1785: class attributes and INPUT_TYPES the UI / workflow JSONs rely on."""
-    from comfy_gen_server_b200 import nodes, samplers
-    for cls in (nodes.KSampler, nodes.KSamplerAdvanced):
-        assert cls.RETURN_TYPES == ("LATENT",) and cls.FUNCTION == "sample" and cls.CATEGORY == "sampling"
-    req = nodes.KSampler.INPUT_TYPES()["required"]
-    assert list(req) == ["model", "seed", "steps", "cfg", "sampler_name", "scheduler", "positive", "negative",
-                         "latent_image", "denoise"]
-    assert req["sampler_name"][0] is samplers.KSampler.SAMPLERS and req["seed"][1]["max"] == 0xffffffffffffffff
-    adv = nodes.KSamplerAdvanced.INPUT_TYPES()["required"]
-    assert list(adv) == ["model", "add_noise", "noise_seed", "steps", "cfg", "sampler_name", "scheduler", "positive",
-                         "negative", "latent_image", "start_at_step", "end_at_step", "return_with_leftover_noise"]
-    assert nodes.NODE_CLASS_MAPPINGS["KSampler"] is nodes.KSampler
+        models.build_model(fam, "cpu", seed=1, dtype=torch.float32)

@@ -31,3 +31,9 @@ def test_two_gpu_latents_match_single_gpu(batch):
     # CFG split: each rank runs a UNet batch of half the size (library GEMM/conv kernels are chosen by shape), so
     # results agree to bf16 noise amplified by CFG 7 over the schedule, not bit for bit.
     assert res["cfg_split"]["cos"] > 0.9995, res
+    # the replayed step graph (NCCL exchange captured inside it) gives exactly what launch-by-launch gives
+    assert res["cfg_split_graph"]["sum"] == res["cfg_split"]["sum"], res
+    if "cfg_split_peer" in res:
+        # exchange fused into the tail kernel (partner's half read over NVLink): bit-equal to the NCCL version
+        assert res["cfg_split_peer"]["sum"] == res["cfg_split"]["sum"], res
+        assert res["cfg_split_peer_graph"]["sum"] == res["cfg_split"]["sum"], res
