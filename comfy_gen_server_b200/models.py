@@ -55,4 +55,11 @@ def build_model(family: str, device, seed=None, dtype=torch.bfloat16, state_dict
             model.diffusion_model.load_state_dict({k: v.to(dtype) for k, v in state_dict.items()})
     model.eval()
     patcher = comfy.model_patcher.ModelPatcher(model, load_device=dev, offload_device=dev)
+    if dev.type == "cuda":
+        # Bring the model into the state every sample() call after the first one sees: the reference's loader moves
+        # the WHOLE BaseModel to the device, model_sampling's sigma table included, and from then on schedules are
+        # computed with the device's log / exp (an ulp away from the host's). Doing it here keeps the first call
+        # comparable with later ones.
+        import comfy.model_management
+        comfy.model_management.load_models_gpu([patcher])
     return patcher, model
