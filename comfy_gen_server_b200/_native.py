@@ -43,6 +43,8 @@ _SIGNATURES = {
     "cgs_sampler_step_dpmpp2m": [_c_void_p] * 3 + [_c_float] * 4 + [_c_void_p, _c_ll, _c_void_p],
     "cgs_cfg_sampler_tail_dev_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                                        _c_void_p, _c_void_p, _c_void_p, _c_ll, _c_ll, _c_void_p],
+    "cgs_cfg_sampler_tail_peer_fwd": [_c_void_p, _c_void_p, _c_int] + [_c_void_p] * 4 + [_c_ll, _c_void_p, _c_float,
+                                      _c_int, _c_float] + [_c_void_p] * 4 + [_c_ll, _c_ll, _c_void_p],
     "cgs_cfg_sampler_tail_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                                    _c_int] + [_c_float] * 4 + [_c_void_p, _c_void_p,
                                                                                _c_ll, _c_ll, _c_void_p],
@@ -591,6 +593,29 @@ def cfg_sampler_tail_dev(x, model_out_uncond, model_out_cond, sigma, cond_scale:
             x.data_ptr(), u_ptr, c_ptr, is_bf16, sigma.data_ptr(), cond_scale, pred_type, sigma_data,
             old_denoised.data_ptr(), step.data_ptr(), denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
     _check(rc, "cgs_cfg_sampler_tail_dev_fwd")
+    return denoised, x_next
+
+
+def cfg_sampler_tail_peer(x, out_local, local_is_cond: bool, recv_data_ptr: int, peer_data_ptr: int,
+                          recv_flags_ptr: int, peer_flags_ptr: int, flag_capacity: int, sigma, cond_scale: float,
+                          pred_type: int, old_denoised, step: torch.Tensor, denoised: torch.Tensor, x_next: torch.Tensor,
+                          sigma_data: float = 1.0):
+    """CFG pair split over two GPUs: exchange of the model-output halves through peer memory + the tail, one launch
+    (cgs_cfg_sampler_tail_peer_fwd). `step`: fp32 [>= 6] = mode, c0..c3, bit pattern of the int32 sequence number."""
+    for name, t in (("peer tail x", x), ("peer tail sigma", sigma), ("peer tail old_denoised", old_denoised),
+                    ("peer tail step", step), ("peer tail denoised", denoised), ("peer tail x_next", x_next)):
+        _flat_f32(name, t)
+    _require_cuda("peer tail model output", out_local, torch.bfloat16)
+    if not out_local.is_contiguous() or out_local.numel() != x.numel() or step.numel() < 6:
+        raise RuntimeError("peer tail: model output must be contiguous bf16 of x's size and step hold 6 floats")
+    B = x.shape[0]
+    per = x.numel() // B if B else 0
+    with _Launch("cfg_sampler_tail", x, float(x.numel()) * 20):
+        rc = load_library().cgs_cfg_sampler_tail_peer_fwd(
+            x.data_ptr(), out_local.data_ptr(), int(bool(local_is_cond)), recv_data_ptr, peer_data_ptr, recv_flags_ptr,
+            peer_flags_ptr, flag_capacity, sigma.data_ptr(), cond_scale, pred_type, sigma_data, old_denoised.data_ptr(),
+            step.data_ptr(), denoised.data_ptr(), x_next.data_ptr(), B, per, _stream(x))
+    _check(rc, "cgs_cfg_sampler_tail_peer_fwd")
     return denoised, x_next
 
 

@@ -136,6 +136,99 @@ tail_kernel(const float* __restrict__ x, const void* __restrict__ out_uncond,
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// CFG pair split across two GPUs: the exchange of the two halves of the model output and the tail, in ONE kernel.
+//
+// Each rank of a pair evaluated one half of the UNet batch (cond or uncond). Both need both halves for
+// cfg_function (comfy/samplers.py:234-247). Instead of a collective followed by the tail kernel, every CTA
+//   1. pushes its chunk of this rank's half into the partner's receive buffer (ordinary 8-byte global stores
+//      through a peer mapping: they cross NVLink once, as posted writes), fences, and raises the partner's flag
+//      for that chunk (release store, system scope);
+//   2. waits for its own flag (acquire load, system scope): the partner's chunk has landed in local memory;
+//   3. runs the tail on (x, its half, the partner's half).
+// Chunk i of one rank pairs with chunk i of the other (same shapes, same grid), so the exchange is pipelined chunk
+// by chunk and needs no grid-wide or cross-GPU barrier. The receive buffer has two slots (step parity): a rank can
+// only be one step ahead of its partner, because its next step needs the partner's push of that step. Flags are the
+// step sequence number and only ever grow. The step's sequence number, sampler mode and coefficients are read from
+// device memory, so the launch is the same for every step and sits inside the replayed step graph.
+// A partner that never arrives trips a watchdog (trap) instead of hanging the GPU.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(256)
+tail_peer_kernel(const float* __restrict__ x, const uint2* __restrict__ out_local, const uint2* recv_data,
+                 uint2* peer_data, const int* recv_flags, int* peer_flags, const float* __restrict__ sigma,
+                 const float* __restrict__ d_old, float* __restrict__ denoised, float* __restrict__ x_next,
+                 long long n4, long long per_sample4, float cond_scale, float sigma_data, int pred_type,
+                 int local_is_cond, const float* __restrict__ dev_step) {
+    const int mode = static_cast<int>(__ldg(dev_step));
+    TailCoef k;
+    k.c0 = __ldg(dev_step + 1);
+    k.c1 = __ldg(dev_step + 2);
+    k.c2 = __ldg(dev_step + 3);
+    k.c3 = __ldg(dev_step + 4);
+    const int seq = __float_as_int(__ldg(dev_step + 5));
+    const long long slot_off = (seq & 1) ? n4 : 0;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < n4;
+
+    uint2 mine = make_uint2(0u, 0u);
+    if (live) {
+        mine = __ldg(out_local + i);
+        peer_data[slot_off + i] = mine;                  // remote store into the partner's receive slot
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        st_release_sys(peer_flags + blockIdx.x, seq + 1);
+        long long t0 = clock64();
+        while (ld_acquire_sys(recv_flags + blockIdx.x) < seq + 1) {
+            if (clock64() - t0 > 60000000000LL) __trap();    // ~30 s: the partner rank is gone
+        }
+    }
+    __syncthreads();
+    if (!live) return;
+    // written by the partner GPU: read past the (non-coherent) L1
+    const uint2 theirs = __ldcv(recv_data + slot_off + i);
+    const uint2 uc = local_is_cond ? theirs : mine;      // uncond half
+    const uint2 cc = local_is_cond ? mine : theirs;      // cond half
+    const float2 u0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uc.x));
+    const float2 u1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uc.y));
+    const float2 c0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&cc.x));
+    const float2 c1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&cc.y));
+    const float ou[4] = {u0.x, u0.y, u1.x, u1.y};
+    const float oc[4] = {c0.x, c0.y, c1.x, c1.y};
+    const float4 xv = __ldg(reinterpret_cast<const float4*>(x) + i);
+    const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+    const float s = __ldg(sigma + i / per_sample4);
+    float d[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float dc = denoise_one(xs[j], oc[j], s, sigma_data, pred_type);
+        const float du = denoise_one(xs[j], ou[j], s, sigma_data, pred_type);
+        d[j] = cfg_one(dc, du, cond_scale);
+    }
+    reinterpret_cast<float4*>(denoised)[i] = make_float4(d[0], d[1], d[2], d[3]);
+    float o[4] = {0.f, 0.f, 0.f, 0.f};
+    if (mode == kTailDpmpp2m) {
+        const float4 ov = __ldg(reinterpret_cast<const float4*>(d_old) + i);
+        o[0] = ov.x; o[1] = ov.y; o[2] = ov.z; o[3] = ov.w;
+    }
+    float4 r;
+    r.x = step_one(mode, xs[0], d[0], o[0], k);
+    r.y = step_one(mode, xs[1], d[1], o[1], k);
+    r.z = step_one(mode, xs[2], d[2], o[2], k);
+    r.w = step_one(mode, xs[3], d[3], o[3], k);
+    reinterpret_cast<float4*>(x_next)[i] = r;
+}
+
 // x (fp32) -> UNet input (bf16), duplicated `copies` times along the batch (uncond, cond halves):
 //   out[c, b, ...] = bf16( x[b, ...] / sqrt(sigma[b]^2 + sigma_data^2) )
 __global__ void __launch_bounds__(256)
@@ -286,4 +379,43 @@ extern "C" int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_unco
     return cgs::launch_tail(x, out_uncond, out_cond, out_is_bf16, sigma, old_denoised, denoised,
                             x_next, batch, per_sample, cond_scale, sigma_data, pred_type, cgs::kTailDpmpp2m,
                             TailCoef{0, 0, 0, 0}, static_cast<cudaStream_t>(stream), step);
+}
+
+// CFG-pair split over two GPUs: exchange + tail in one launch (see tail_peer_kernel). All `recv_*` pointers are this
+// GPU's own memory, `peer_*` the partner's receive buffer / flags through a peer mapping. Model outputs are bf16.
+// step[0..4] as in cgs_cfg_sampler_tail_dev_fwd, step[5] = the bit pattern of the int32 sequence number of this
+// exchange (0, 1, 2, ... identical on both ranks). flags: one int32 per 1024 latent elements, zero-initialised once.
+extern "C" int cgs_cfg_sampler_tail_peer_fwd(const float* x, const void* out_local, int local_is_cond,
+                                             const void* recv_data, void* peer_data, const int* recv_flags,
+                                             int* peer_flags, long long flag_capacity, const float* sigma,
+                                             float cond_scale, int pred_type, float sigma_data,
+                                             const float* old_denoised, const float* step, float* denoised,
+                                             float* x_next, long long batch, long long per_sample, void* stream) {
+    using namespace cgs;
+    if (!x || !out_local || !recv_data || !peer_data || !recv_flags || !peer_flags || !sigma || !old_denoised ||
+        !step || !denoised || !x_next) {
+        set_last_error("cfg_sampler_tail_peer: null pointer argument");
+        return kBadArgument;
+    }
+    int rc = check_tail_shape("cfg_sampler_tail_peer", batch, per_sample);
+    if (rc != kOk) return rc;
+    if (pred_type != 0 && pred_type != 1) {
+        set_last_error("cfg_sampler_tail_peer: pred_type %d (0 = EPS, 1 = V_PREDICTION)", pred_type);
+        return kBadArgument;
+    }
+    const long long n4 = batch * per_sample / 4;
+    if (n4 == 0) return kOk;
+    const long long grid = (n4 + 255) / 256;
+    // every CTA waits for its partner CTA while holding its SM slot: all of them must be resident at once
+    if (grid > flag_capacity || grid > (long long)sm_count() * 8) {
+        set_last_error("cfg_sampler_tail_peer: %lld chunks exceed the flag capacity %lld or the resident-CTA limit %lld",
+                       grid, flag_capacity, (long long)sm_count() * 8);
+        return kUnsupportedShape;
+    }
+    tail_peer_kernel<<<(unsigned)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, static_cast<const uint2*>(out_local), static_cast<const uint2*>(recv_data), static_cast<uint2*>(peer_data),
+        recv_flags, peer_flags, sigma, old_denoised, denoised, x_next, n4, per_sample / 4, cond_scale, sigma_data,
+        pred_type, local_is_cond, step);
+    CGS_CUDA_CHECK(cudaGetLastError());
+    return kOk;
 }

@@ -197,9 +197,13 @@ class FusedDenoise:
         sigma_vec, t_vec, _ = self._sigma_and_t(i, sigma_f, x)
         xc = _native.unet_input(x, sigma_vec, self.copies, float(self.ms.sigma_data))
         out = self._unet(xc, t_vec, self.context, self.y, sigma_vec)
-        out_u, out_c = self._halves(out, x.shape[0])
-        res = _native.cfg_sampler_tail(x, out_u, out_c, sigma_vec, self.cfg, self.pred_type, old_denoised,
-                                       sampler, c0, c1, c2, c3, float(self.ms.sigma_data))
+        if self.split is not None and self.split.fuses_tail:
+            res = self.split.tail_eager(x, out, sigma_vec, self.cfg, self.pred_type, old_denoised, sampler,
+                                        c0, c1, c2, c3, float(self.ms.sigma_data))
+        else:
+            out_u, out_c = self._halves(out, x.shape[0])
+            res = _native.cfg_sampler_tail(x, out_u, out_c, sigma_vec, self.cfg, self.pred_type, old_denoised,
+                                           sampler, c0, c1, c2, c3, float(self.ms.sigma_data))
         if probe:
             self.probe = ((time.perf_counter() - t_host) * 1e3, ev)
             ev[1].record()
@@ -255,9 +259,13 @@ class FusedDenoise:
         def body():
             xc = _native.unet_input(g["X"], sigma_vec, copies, sigma_data)
             out = self._unet(xc, t_vec, g["CTX"], g["Y"], sigma_vec)
-            out_u, out_c = self._halves(out, b)
-            _native.cfg_sampler_tail_dev(g["X"], out_u, out_c, sigma_vec, self.cfg, self.pred_type, g["OLD"], step,
-                                         g["DEN"], g["XN"], sigma_data)
+            if self.split is not None and self.split.fuses_tail:
+                self.split.tail_dev(g["X"], out, sigma_vec, self.cfg, self.pred_type, g["OLD"], step, g["DEN"],
+                                    g["XN"], sigma_data)
+            else:
+                out_u, out_c = self._halves(out, b)
+                _native.cfg_sampler_tail_dev(g["X"], out_u, out_c, sigma_vec, self.cfg, self.pred_type, g["OLD"],
+                                             step, g["DEN"], g["XN"], sigma_data)
             g["OLD"].copy_(g["DEN"])                     # the next step's old_denoised
 
         before = dict(_native.LAUNCHES)
@@ -346,6 +354,8 @@ class FusedDenoise:
         row[:b] = sigma_f
         row[b:b + b * copies] = t
         row[b + b * copies:b + b * copies + 5] = torch.tensor([float(sampler), c0, c1, c2, c3])
+        if self.split is not None and self.split.fuses_tail:       # sequence number of this pair exchange
+            row[b + b * copies + 5:b + b * copies + 6].view(torch.int32)[0] = self.split.next_seq(x.numel(), x.device)
         g["P"].copy_(row, non_blocking=True)
         g["X"].copy_(x)
         if sampler == 3 and old_denoised is not None and old_denoised is not g["last_den"]:

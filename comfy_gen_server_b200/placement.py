@@ -109,6 +109,7 @@ class PairExchange:
     """How the two ranks of a CFG pair trade their halves of the model output each step (guider.FusedDenoise calls
     exchange(out) -> (uncond, cond)). This one is the plain NCCL version."""
     graph_capturable = True
+    fuses_tail = False
 
     def __init__(self, placement: Placement, group):
         self.placement, self.group = placement, group
@@ -126,6 +127,77 @@ class PairExchange:
 
     def key(self):
         return ("nccl", self.placement.role, self.placement.pair)
+
+
+_peer_buffers: dict = {}
+
+
+class PeerExchange(PairExchange):
+    """The exchange fused into the tail kernel (cgs_cfg_sampler_tail_peer_fwd): each rank's kernel pushes its half of
+    the model output straight into the partner's receive buffer over NVLink (symmetric memory: every rank allocates
+    the same buffer and maps the partner's), flags it chunk by chunk, and consumes the partner's half as it lands --
+    no collective launch between the UNet and the tail, and nothing in the step that a CUDA graph cannot hold.
+    Bit-identical to the NCCL version (same kernel arithmetic on the same bf16 halves)."""
+    fuses_tail = True
+    graph_capturable = True
+    FLAG_CAPACITY = 4096                      # chunks of 1024 latent elements: up to 4 Mi elements per exchange
+
+    def __init__(self, placement: Placement, group):
+        super().__init__(placement, group)
+        self._buf = None
+        self._ring = None
+
+    def _buffers(self, n_elems: int, device):
+        """Symmetric allocation [flags | slot 0 | slot 1] for exchanges of n_elems bf16 values, made once per
+        (pair, size) and kept: the rendezvous is a collective, and the sequence number lives with the buffers."""
+        key = (self.placement.pair, n_elems, str(device))
+        buf = _peer_buffers.get(key)
+        if buf is None:
+            import torch.distributed._symmetric_memory as symm_mem
+            flag_bytes = self.FLAG_CAPACITY * 4
+            total = flag_bytes + 2 * n_elems * 2
+            t = symm_mem.empty(total, dtype=torch.uint8, device=device)
+            t.zero_()
+            hdl = symm_mem.rendezvous(t, self.group)
+            me = dist.get_rank(self.group)
+            ptrs = list(hdl.buffer_ptrs)
+            torch.cuda.synchronize(device)
+            dist.barrier(group=self.group)              # both sides zeroed before anyone raises a flag
+            buf = {"tensor": t, "handle": hdl, "seq": 0, "flag_bytes": flag_bytes,
+                   "local": ptrs[me], "peer": ptrs[1 - me]}
+            _peer_buffers[key] = buf
+        return buf
+
+    def next_seq(self, n_elems: int, device) -> int:
+        buf = self._buffers(n_elems, device)
+        s = buf["seq"]
+        buf["seq"] = s + 1
+        return s
+
+    def tail_dev(self, x, out_local, sigma_vec, cfg, pred_type, old, step, denoised, x_next, sigma_data):
+        """step: device fp32 row (mode, c0..c3, sequence-number bits) -- see next_seq()."""
+        from . import _native
+        buf = self._buffers(x.numel(), x.device)
+        fb = buf["flag_bytes"]
+        return _native.cfg_sampler_tail_peer(
+            x, out_local, self.placement.role == "cond", buf["local"] + fb, buf["peer"] + fb, buf["local"], buf["peer"],
+            self.FLAG_CAPACITY, sigma_vec, cfg, pred_type, old, step, denoised, x_next, sigma_data)
+
+    def tail_eager(self, x, out_local, sigma_vec, cfg, pred_type, old, sampler, c0, c1, c2, c3, sigma_data):
+        if self._ring is None:
+            self._ring = (torch.zeros(256, 8, dtype=torch.float32).pin_memory(), [0])
+        rows, pos = self._ring
+        row = rows[pos[0] % rows.shape[0]]               # a pinned row per step: not rewritten while in flight
+        pos[0] += 1
+        row[:5] = torch.tensor([float(sampler), c0, c1, c2, c3])
+        row[5:6].view(torch.int32)[0] = self.next_seq(x.numel(), x.device)
+        step = row.to(x.device, non_blocking=True)
+        den, xn = torch.empty_like(x), torch.empty_like(x)
+        return self.tail_dev(x, out_local, sigma_vec, cfg, pred_type, x if old is None else old, step, den, xn,
+                             sigma_data)
+
+    def key(self):
+        return ("peer", self.placement.role, self.placement.pair)
 
 
 _split_cls = None

@@ -263,6 +263,27 @@ int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_uncond, const v
                                  const float* step, float* denoised, float* x_next,
                                  long long batch, long long per_sample, void* stream);
 
+/*
+ * The same tail for a cond / uncond pair that is split across two GPUs (multi-GPU placement):
+ * the exchange of the two halves of the model output and cfg_function + sampler update (comfy/samplers.py:234-247,
+ * comfy/k_diffusion/sampling.py:137-143, 583-592) in ONE launch, instead of a collective followed by the tail.
+ * This rank evaluated `out_local` (bf16; the cond half when local_is_cond != 0, else the uncond half). Every CTA
+ * pushes its chunk of out_local into the partner's receive buffer `peer_data` (a peer mapping of the partner's
+ * `recv_data`; plain global stores over NVLink), raises `peer_flags[chunk]`, waits for `recv_flags[chunk]` and then
+ * reads the partner's half from its own `recv_data`.
+ *   recv_data / peer_data   2 slots x (batch * per_sample) bf16 (slot = sequence number & 1)
+ *   recv_flags / peer_flags int32 per chunk of 1024 latent elements (`flag_capacity` of them), zeroed once
+ *   step[0..4] as in cgs_cfg_sampler_tail_dev_fwd; step[5] = bit pattern of the int32 sequence number of this
+ *   exchange, counted 0, 1, 2, ... identically on both ranks for the life of the buffers.
+ * All chunks (batch * per_sample / 1024) must be resident at once: CGS_UNSUPPORTED_SHAPE beyond 8 x SM count.
+ * A partner that does not arrive within ~30 s traps (the launch fails) instead of hanging the GPU.
+ */
+int cgs_cfg_sampler_tail_peer_fwd(const float* x, const void* out_local, int local_is_cond,
+                                  const void* recv_data, void* peer_data, const int* recv_flags, int* peer_flags,
+                                  long long flag_capacity, const float* sigma, float cond_scale, int pred_type,
+                                  float sigma_data, const float* old_denoised, const float* step, float* denoised,
+                                  float* x_next, long long batch, long long per_sample, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

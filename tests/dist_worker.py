@@ -51,7 +51,13 @@ def main():
                          "sum": float(out.double().sum())}
     if rank == 0:
         print("RESULT " + json.dumps(res), flush=True)
-    dist.destroy_process_group()
+    # captured step graphs hold NCCL kernels of the pair communicators: drop them before the communicators go, and do
+    # not let a slow communicator teardown keep the test waiting
+    patcher.model.__dict__.pop("_cgs_step_graphs", None)
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":
