@@ -36,6 +36,7 @@ _SIGNATURES = {
     "cgs_transpose_add_fwd": [_c_void_p] * 3 + [_c_int] * 3 + [_c_void_p],
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
+    "cgs_gemm_set_variant": [_c_int],
     "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
     "cgs_cfg_denoise_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                               _c_ll, _c_ll, _c_void_p],

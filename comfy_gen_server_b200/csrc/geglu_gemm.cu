@@ -8,24 +8,31 @@
 // The same kernel (EPI_LINEAR) serves plain Linear layers  y = x W^T (+ b) (+ residual)
 // (reference comfy/ops.py:40-52), used for to_q/to_k/to_v/to_out/ff.net.2/proj_in/proj_out.
 //
-// Structure (one persistent CTA per SM, 576 threads):
-//   warp 0       TMA producer: A tile [128 x 64] and B tile [256 x 64] per k-block, 4-stage ring
-//   warp 1       TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=256, K=16 x 4 per block)
-//   warps 2..17  epilogue (4 warps per TMEM lane quadrant, each owning a 32/64-column slice):
-//                tcgen05.ld accumulator -> bias/GELU/gate -> bf16 -> global.
+// Structure (persistent, 576 threads per CTA):
+//   warp 0       TMA producer
+//   warp 1       TMEM allocator + single-thread tcgen05.mma issuer
+//   warps 2..17  epilogue (4 warps per TMEM lane quadrant, each owning a 32-column slice of a 128-column pass):
+//                tcgen05.ld accumulator -> bias / GELU / gate / residual -> bf16 -> swizzled SMEM staging -> TMA store.
+// Two instantiations of the mainloop:
+//   PAIR = false  one CTA per SM, tile M128 x N256: A [128 x 64] + B [256 x 64] per k-block, 4-stage ring.
+//   PAIR = true   CTA pairs (cluster of 2, cta_group::2), tile M256 x N256 per pair: each CTA stages its own
+//                 A [128 x 64] and HALF of B [128 x 64] (32 KiB per k-block instead of 48, 6-stage ring) and owns the
+//                 accumulators of its 128 rows. The first round's mainloop was bound by the L2 -> SMEM operand feed
+//                 (narrower tiles lost exactly in proportion to their arithmetic intensity, profiles/r01_*): halving
+//                 the B traffic per CTA is the fix. The leader CTA issues the MMAs; its commits arrive on the
+//                 barriers of both CTAs; the peer's TMA credits its bytes to the leader's `full` barrier and its
+//                 epilogue warps arrive on the leader's `tempty` barrier through the cluster's shared window.
+//                 Used when the problem has enough M256 x N256 tiles to fill the 74 pairs.
 // 16 epilogue warps, not 4: the first version (4 warps, erff) ran one warp per scheduler at IPC 0.24 and
-// needed 23.8 k cycles per tile against 5.1 k cycles of MMA (ncu, profiles/r01_*): latency-bound. Four
-// warps per scheduler hide the TMEM-load / MUFU / store latencies, and a branch-free erf halves the
-// instruction count. Tiles are walked in groups of 8 M-blocks x all N-blocks so the A panel of a group
-// stays in L2 while its N-blocks are produced (the M-fastest order re-read A from DRAM 9x).
-// Output goes registers -> 128-byte-swizzled SMEM staging tile -> TMA store: with direct row-strided
-// 16-byte global stores the kernel was store-bound (872 TFLOP/s; 1645 with the stores removed).
+// needed 23.8 k cycles per tile against 5.1 k cycles of MMA (ncu, profiles/r01_*): latency-bound. Tiles are walked
+// in groups of 8 M-blocks x all N-blocks so the A panel of a group stays in L2 while its N-blocks are produced.
 // Accumulators are double-buffered in TMEM (2 x 256 fp32 columns = all 512 columns), so the
 // epilogue of tile i overlaps the MMAs of tile i+1.
 //
 // For GEGLU the B tile's rows [0,128) come from W rows [n0, n0+128) (value half) and rows
 // [128,256) from W rows [N+n0, N+n0+128) (gate half): one N=256 MMA produces both halves of
-// the same 128 output columns side by side in TMEM.
+// the same 128 output columns side by side in TMEM. (With CTA pairs the leader stages the value rows and the peer
+// the gate rows.)
 //
 // Tensor-core bound. Algorithmic FLOPs = 2 * M * K * (2N) for GEGLU, 2 * M * K * N for linear.
 #include "common.cuh"
@@ -37,21 +44,26 @@
 namespace cgs {
 
 namespace gemm {
-constexpr int BM = 128;
+constexpr int BM = 128;                       // rows per CTA
 constexpr int BK = 64;
-constexpr int BN_HALF = 128;   // rows per B TMA box
+constexpr int BN_HALF = 128;                  // rows per B TMA box
 constexpr int UMMA_N = 256;
-constexpr int STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;          // 16 KiB
-constexpr int B_BYTES = UMMA_N * BK * 2;      // 32 KiB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int OUT_BOX_BYTES = BM * 128;                  // [128 rows x 64 bf16], 128-byte swizzle
 constexpr int OUT_STAGE_BYTES = 2 * OUT_BOX_BYTES;       // 128 output columns per pass
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGE_BYTES + 256 + 1024;  // + barriers + slack
 constexpr int EPI_WARPS = 16;
 constexpr int THREADS = (2 + EPI_WARPS) * 32;
 constexpr int GROUP_M = 8;
 enum { EPI_LINEAR = 0, EPI_GEGLU = 1 };
+
+template <bool PAIR>
+struct Cfg {
+    static constexpr int STAGES = PAIR ? 6 : 4;
+    static constexpr int B_BYTES = (PAIR ? BN_HALF : UMMA_N) * BK * 2;       // per CTA: 16 / 32 KiB
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TILE_M = PAIR ? 2 * BM : BM;                         // rows per tile (per pair / per CTA)
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGE_BYTES + 256 + 1024;  // + barriers + slack
+};
 }  // namespace gemm
 
 // Exact-erf GELU, 0.5 x (1 + erf(x / sqrt 2)), with erf from Abramowitz & Stegun 7.1.26
@@ -84,15 +96,18 @@ struct alignas(16) BF8 {
     __nv_bfloat162 v[4];
 };
 
-template <int EPI>
+template <int EPI, bool PAIR>
 __global__ void __launch_bounds__(gemm::THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
             __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr) {
+    using namespace gemm;
+    using C = Cfg<PAIR>;
+    constexpr int STAGES = C::STAGES;
+    constexpr int STAGE_BYTES = C::STAGE_BYTES;
     // timing experiments with wrong results are compile-time only (-DCGS_GEMM_EXPT=<bits>, tools/gemm_dbg.sh builds a
     // private copy of the library): 1 no GELU, 2 no stores, 4 reload A instead of B, 8 one MMA per k-block
     constexpr int dbg = CGS_GEMM_EXPT;
-    using namespace gemm;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
@@ -105,7 +120,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int tiles_m = (M + BM - 1) / BM;
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;        // 0 = leader of the pair
+    const int worker = PAIR ? (blockIdx.x >> 1) : blockIdx.x;   // pair (or CTA) index
+    const int workers = PAIR ? (gridDim.x >> 1) : gridDim.x;
+    const int tiles_m = (M + C::TILE_M - 1) / C::TILE_M;
     const int tiles_n = (EPI == EPI_GEGLU) ? (N / BN_HALF) : ((N + UMMA_N - 1) / UMMA_N);
     const int num_tiles = tiles_m * tiles_n;
     const int kblocks = (K + BK - 1) / BK;
@@ -123,16 +141,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             for (int i = 0; i < 2; ++i) {
                 mbar_init(&tfull[i], 1);
-                mbar_init(&tempty[i], EPI_WARPS);
+                mbar_init(&tempty[i], PAIR ? 2 * EPI_WARPS : EPI_WARPS);   // pair: both CTAs' epilogue warps
             }
             fence_mbar_init();
         }
         __syncwarp();
-        tmem_alloc(tmem_slot, 512);
-        tmem_relinquish();
+        if (PAIR) {
+            tmem_alloc_pair(tmem_slot, 512);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc(tmem_slot, 512);
+            tmem_relinquish();
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all(); else __syncthreads();      // barriers of both CTAs initialised before any remote use
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -141,24 +164,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = worker; t < num_tiles; t += workers) {
                 int mb, nb;
                 tile_coords(t, tiles_m, tiles_n, mb, nb);
-                const int m0 = mb * BM;
+                const int m0 = mb * C::TILE_M + (int)rank * BM;
                 const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N;
                 const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : nb * UMMA_N + BN_HALF;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
-                    mbar_expect_tx(&full[stage], STAGE_BYTES);
-                    tma_load_2d(sa, &tmA, &full[stage], kb * BK, m0);
-                    if (dbg & 4) {   // experiment: reload the A box instead of B (1/3 of the distinct L2 lines)
-                        tma_load_2d(sb, &tmA, &full[stage], kb * BK, m0);
-                        tma_load_2d(sb + BN_HALF * BK * 2, &tmA, &full[stage], kb * BK, m0);
+                    if (PAIR) {
+                        // both CTAs' bytes are credited to the leader's barrier; the leader announces them
+                        if (rank == 0) mbar_expect_tx(&full[stage], 2 * STAGE_BYTES);
+                        tma_load_2d_pair(sa, &tmA, &full[stage], kb * BK, m0);
+                        tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, rank == 0 ? row0 : row1);
                     } else {
-                        tma_load_2d(sb, &tmB, &full[stage], kb * BK, row0);
-                        tma_load_2d(sb + BN_HALF * BK * 2, &tmB, &full[stage], kb * BK, row1);
+                        mbar_expect_tx(&full[stage], STAGE_BYTES);
+                        tma_load_2d(sa, &tmA, &full[stage], kb * BK, m0);
+                        if (dbg & 4) {   // experiment: reload the A box instead of B (1/3 of the distinct L2 lines)
+                            tma_load_2d(sb, &tmA, &full[stage], kb * BK, m0);
+                            tma_load_2d(sb + BN_HALF * BK * 2, &tmA, &full[stage], kb * BK, m0);
+                        } else {
+                            tma_load_2d(sb, &tmB, &full[stage], kb * BK, row0);
+                            tma_load_2d(sb + BN_HALF * BK * 2, &tmB, &full[stage], kb * BK, row1);
+                        }
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -166,14 +196,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ------------------------------ MMA issuer --------------------------------
-        if (elect_one()) {
-            const uint32_t idesc = umma_idesc_bf16(BM, UMMA_N, 0);
+        // ------------------------------ MMA issuer (leader CTA only for pairs) ------
+        if (rank == 0 && elect_one()) {
+            const uint32_t idesc = umma_idesc_bf16(C::TILE_M, UMMA_N, 0);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = worker; t < num_tiles; t += workers) {
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * UMMA_N;
@@ -186,13 +216,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
                         // +32 bytes per k-step inside the 128-byte swizzle row (>> 4 == 2)
-                        if (!(dbg & 8) || k == 0)
-                            umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        if (!(dbg & 8) || k == 0) {
+                            if (PAIR) umma_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                            else umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        }
                     }
-                    tc_commit(&empty[stage]);
+                    if (PAIR) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                tc_commit(&tfull[acc]);
+                if (PAIR) tc_commit_pair(&tfull[acc]); else tc_commit(&tfull[acc]);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -208,12 +240,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         uint8_t* my_stage = out_stage + (cg >> 1) * OUT_BOX_BYTES + row_in_tile * 128;
         const int chunk0 = (cg & 1) * 4;
         const int sw = row_in_tile & 7;
+        // the accumulator buffer goes back to the MMA issuer: its `tempty` barrier lives in the leader CTA
+        const uint32_t tempty_addr0 = PAIR ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;
+        auto release_acc = [&](int acc) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (PAIR) mbar_arrive_cluster(tempty_addr0 + acc * 8);
+                else mbar_arrive(&tempty[acc]);
+            }
+        };
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        for (int t = worker; t < num_tiles; t += workers) {
             int mb, nb;
             tile_coords(t, tiles_m, tiles_n, mb, nb);
-            const int row = mb * BM + row_in_tile;
+            const int row_base = mb * C::TILE_M + (int)rank * BM;
+            const int row = row_base + row_in_tile;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * UMMA_N + (static_cast<uint32_t>(quad * 32) << 16);
@@ -229,9 +272,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     tmem_ld_x32(taddr + BN_HALF + cg * 32, g);
                     tmem_wait_ld();
                     // accumulator is in registers: hand the TMEM buffer back to the MMA warp now
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&tempty[acc]);
+                    release_acc(acc);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         BF8 bv, bg;
@@ -260,11 +301,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     uint32_t v[32];
                     tmem_ld_x32(taddr + pass * 128 + cg * 32, v);
                     tmem_wait_ld();
-                    if (pass == PASSES - 1) {
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&tempty[acc]);
-                    }
+                    if (pass == PASSES - 1) release_acc(acc);
                     const bool col_ok = col < N;      // N % 32 == 0: a 32-column group is all in or all out
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
@@ -297,10 +334,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     *reinterpret_cast<BF8*>(my_stage + (((chunk0 + q) ^ sw) << 4)) = o[q];
                 fence_proxy_async_smem();
                 named_bar_sync(1, EPI_THREADS);
-                if (store_leader && !(dbg & 2)) {
+                if (store_leader && !(dbg & 2) && row_base < M) {
                     const int c0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N + pass * 128;
-                    if (c0 < N) tma_store_2d(&tmO, out_stage, c0, mb * BM);
-                    if (c0 + 64 < N) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, mb * BM);
+                    if (c0 < N) tma_store_2d(&tmO, out_stage, c0, row_base);
+                    if (c0 + 64 < N) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, row_base);
                     tma_store_commit();
                 }
             }
@@ -310,9 +347,45 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
 
     tc_fence_before();
-    __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 512);
+    if (PAIR) cluster_sync_all(); else __syncthreads();       // nobody leaves while its partner still needs it
+    if (warp == 1) {
+        if (PAIR) tmem_dealloc_pair(tmem_base, 512);
+        else tmem_dealloc(tmem_base, 512);
+    }
 }
+
+template <int EPI, bool PAIR>
+static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
+                          const __nv_bfloat16* bp, const __nv_bfloat16* rp, __nv_bfloat16* op, int M, int N, int K,
+                          int ldo, int ldr, long long tiles, cudaStream_t stream) {
+    using namespace gemm;
+    using C = Cfg<PAIR>;
+    auto kern = gemm_kernel<EPI, PAIR>;
+    CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    const int sms = sm_count();
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    if (PAIR) {
+        const long long pairs = tiles < sms / 2 ? tiles : sms / 2;
+        cfg.gridDim = dim3((unsigned)(2 * pairs));
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    } else {
+        cfg.gridDim = dim3((unsigned)(tiles < sms ? tiles : sms));
+    }
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = stream;
+    CGS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, bp, rp, op, M, N, K, ldo, ldr));
+    return kOk;
+}
+
+// which mainloop: 0 = automatic, 1 = one CTA per tile (M128), 2 = CTA pairs (M256). (tools/kernel_bench.py compares)
+static int g_gemm_force_variant = 0;
 
 static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
                        const void* residual, void* out, long long M, int N, int K, long long lda,
@@ -370,26 +443,24 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
         int rc = make_tmap_bf16(&tmO, out, 2, dims, strides, box);
         if (rc != kOk) return rc;
     }
-    const int tiles_m = (int)((M + BM - 1) / BM);
     const int tiles_n = (epi == EPI_GEGLU) ? N / BN_HALF : (N + UMMA_N - 1) / UMMA_N;
-    const long long tiles = (long long)tiles_m * tiles_n;
-    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    const long long tiles1 = ((M + BM - 1) / BM) * tiles_n;
+    const long long tiles2 = ((M + 2 * BM - 1) / (2 * BM)) * tiles_n;
+    // CTA pairs need enough M256 tiles to keep the 74 pairs busy for a few rounds; below that the M128 tiling has
+    // twice the parallelism
+    const int pairs = sm_count() / 2;
+    bool pair = tiles2 >= 3LL * pairs;
+    if (g_gemm_force_variant == 1) pair = false;
+    if (g_gemm_force_variant == 2) pair = true;
     auto bp = static_cast<const __nv_bfloat16*>(bias);
     auto rp = static_cast<const __nv_bfloat16*>(residual);
     auto op = static_cast<__nv_bfloat16*>(out);
     if (epi == EPI_GEGLU) {
-        CGS_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<EPI_GEGLU>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        gemm_kernel<EPI_GEGLU><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K,
-                                                                      (int)ldo, (int)ldr);
-    } else {
-        CGS_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<EPI_LINEAR>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        gemm_kernel<EPI_LINEAR><<<grid, THREADS, SMEM_BYTES, stream>>>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K,
-                                                                       (int)ldo, (int)ldr);
+        return pair ? launch_variant<EPI_GEGLU, true>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
+                    : launch_variant<EPI_GEGLU, false>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
     }
-    CGS_CUDA_CHECK(cudaGetLastError());
-    return kOk;
+    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
+                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
 }
 
 }  // namespace cgs
@@ -406,4 +477,15 @@ extern "C" int cgs_linear_fwd(const void* x, const void* w, const void* bias, co
                               long long ldy, long long ldr, void* stream) {
     return cgs::launch_gemm(cgs::gemm::EPI_LINEAR, x, w, bias, residual, y, M, N, K, lda, ldw, ldy,
                             ldr, static_cast<cudaStream_t>(stream));
+}
+
+// Developer switch for the micro-benchmarks: 0 automatic, 1 always one CTA per tile, 2 always CTA pairs. Both
+// mainloops compute the same products in the same order per output element; results are identical.
+extern "C" int cgs_gemm_set_variant(int variant) {
+    if (variant < 0 || variant > 2) {
+        cgs::set_last_error("gemm_set_variant: %d (0 automatic, 1 single CTA, 2 CTA pairs)", variant);
+        return cgs::kBadArgument;
+    }
+    cgs::g_gemm_force_variant = variant;
+    return cgs::kOk;
 }

@@ -264,6 +264,13 @@ int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_uncond, const v
                                  long long batch, long long per_sample, void* stream);
 
 /*
+ * Tuning switch for the micro-benchmarks (no counterpart in the reference): which mainloop cgs_geglu_gemm_fwd /
+ * cgs_linear_fwd use -- 0 automatic (default), 1 one CTA per M128 x N256 tile, 2 CTA pairs (cta_group::2) on
+ * M256 x N256 tiles. Both compute every output element from the same products in the same order: results are identical.
+ */
+int cgs_gemm_set_variant(int variant);
+
+/*
  * The same tail for a cond / uncond pair that is split across two GPUs (multi-GPU placement):
  * the exchange of the two halves of the model output and cfg_function + sampler update (comfy/samplers.py:234-247,
  * comfy/k_diffusion/sampling.py:137-143, 583-592) in ONE launch, instead of a collective followed by the tail.

@@ -356,6 +356,30 @@ def test_geglu_vs_oracle(M, K, Nn):
     assert (y - ref).abs().max() <= ulp_tol(ref)
 
 
+@pytest.mark.parametrize("M,K,Nn", [(256, 64, 128), (300, 320, 1280), (4096 + 17, 640, 2560), (1, 128, 128),
+                                    (130, 1280, 256), (16384, 1280, 1280)])
+def test_gemm_cta_pair_mainloop_equals_single_cta(M, K, Nn):
+    """The cta_group::2 mainloop (M256 tiles on CTA pairs, half of B per CTA) against the one-CTA mainloop and the
+    oracle, for GEGLU and for linear + bias + residual, incl. M that leaves the pair's second CTA partly or wholly
+    empty. Same products, same order per output element: bit-equal."""
+    n = N()
+    lib = n.load_library()
+    x, w, b = bf(randn((M, K), 1)), bf(randn((2 * Nn, K), 2, K ** -0.5)), bf(randn((2 * Nn,), 3, 0.1))
+    r = bf(randn((M, Nn), 4))
+    try:
+        assert lib.cgs_gemm_set_variant(1) == 0
+        g1, l1 = n.geglu(x, w, b), n.linear(x, w[:Nn], b[:Nn], residual=r)
+        assert lib.cgs_gemm_set_variant(2) == 0
+        g2, l2 = n.geglu(x, w, b), n.linear(x, w[:Nn], b[:Nn], residual=r)
+    finally:
+        lib.cgs_gemm_set_variant(0)
+    ref = O.geglu(x.float().cpu(), w.float().cpu(), b.float().cpu())
+    assert (g2.float().cpu() - ref).abs().max() <= ulp_tol(ref)
+    assert torch.equal(g1, g2) and torch.equal(l1, l2)
+    ref_l = O.linear(x.float().cpu(), w[:Nn].float().cpu(), b[:Nn].float().cpu()) + r.float().cpu()
+    assert (l2.float().cpu() - ref_l).abs().max() <= ulp_tol(ref_l)
+
+
 def test_geglu_golden():
     g = load_golden("blocks")
     from comfy_gen_server_b200 import unet_config as uc
