@@ -350,6 +350,7 @@ def run_ours(args):
         attn_steps = min(args.steps, 6)
         attn_ms, attn_flops, attn_n = family_pass("attention", attn_steps)
         ln_ms, ln_bytes, ln_n = family_pass("add_layernorm", min(args.steps, 3))
+        pln_ms, pln_bytes, pln_n = family_pass("layernorm", min(args.steps, 3))
 
         # ---- end-to-end leg: public API, pinned host buffers -> final latents on the host -------
         noise_h, latent_h = noise.pin_memory(), latent.pin_memory()
@@ -398,6 +399,7 @@ def run_ours(args):
         tf = geglu_flops / (geglu_ms * 1e-3) / 1e12 if geglu_ms > 0 else 0.0
         atf = attn_flops / (attn_ms * 1e-3) / 1e12 if attn_ms > 0 else 0.0
         lnbw = ln_bytes / (ln_ms * 1e-3) / 1e9 if ln_ms > 0 else 0.0
+        plnbw = pln_bytes / (pln_ms * 1e-3) / 1e9 if pln_ms > 0 else 0.0
         peak_tf = peaks["bf16_tflops_sustained"]
         ncu_gemm = load_traffic("gemm_kernel")
         line = {
@@ -425,7 +427,12 @@ def run_ours(args):
                                    "ms_in_kernel_per_step": attn_ms / attn_steps},
             "roofline_add_layernorm": {"kernel": "layernorm_kernel<ADD> (cgs_add_layernorm_fwd)", "bound": "hbm",
                                        "achieved": lnbw, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                       "frac": lnbw / peaks["hbm_gbs"], "launches_timed": ln_n},
+                                       "frac": lnbw / peaks["hbm_gbs"], "launches_timed": ln_n,
+                                       "ms_in_kernel_per_step": ln_ms / min(args.steps, 3)},
+            "roofline_layernorm": {"kernel": "layernorm_stream_kernel (cgs_layernorm_fwd)", "bound": "hbm",
+                                   "achieved": plnbw, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                   "frac": plnbw / peaks["hbm_gbs"], "launches_timed": pln_n,
+                                   "ms_in_kernel_per_step": pln_ms / min(args.steps, 3)},
         }
         if lib_base is not None:
             line["gpu_library_baseline"] = lib_base

@@ -316,7 +316,8 @@ def _group_norm_nhwc(x, weight, bias, groups, eps, silu, add_nc):
 
 # Switches for tools/ablation.py: each one sends an op back to the library call it replaced, so that the step-time value
 # of a kernel can be measured inside one process on one GPU (box-to-box variation is larger than most of them).
-FEATURES = {"residual_add": True, "cat_channels": True, "upsample2x": True, "fold_conv_bias": True}
+FEATURES = {"residual_add": True, "cat_channels": True, "upsample2x": True, "fold_conv_bias": True,
+            "native_linears": True}
 
 
 def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:

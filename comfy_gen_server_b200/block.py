@@ -50,15 +50,46 @@ def _qkv_weight(attn):
     return attn.__dict__["_cgs_qkv_w"]
 
 
+# Which Linear layers of the fast path run on the tcgen05 GEMM of this library and which stay on cuBLASLt, by measurement
+# on the SDXL shapes (profiles/r02_kernel_bench.json): with CTA pairs (K >= 1024) the GEMM is 7 % ahead of cuBLASLt on
+# the fused QKV projection; on the square projections it is 10-15 % behind, which the epilogue more than pays back
+# where it fuses the block's residual add (`x += n` disappears from the LayerNorm that follows). Below ~8 k rows (one or
+# two images per GPU) there are too few tiles for 148 SMs and cuBLASLt's split-K kernels win by up to 2x.
+NATIVE_LINEAR_MIN_ROWS = 8192
+
+
+def _rows(x) -> int:
+    return x.numel() // x.shape[-1]
+
+
+def _gemm_shape_ok(weight) -> bool:
+    return weight.shape[0] % 32 == 0 and weight.shape[1] % 8 == 0
+
+
+def project(x, weight, bias=None, prefer_native=False):
+    """x W^T (+ bias): the library GEMM where it is the faster one (see above), cuBLASLt otherwise."""
+    if prefer_native and _rows(x) >= NATIVE_LINEAR_MIN_ROWS and weight.shape[1] >= 1024 and _gemm_shape_ok(weight) \
+            and _native.FEATURES["native_linears"]:
+        return _native.linear(x, weight, bias)
+    return torch.nn.functional.linear(x, weight, bias)
+
+
+def project_add_(x, a, lin):
+    """x += lin(a) in place (the block's residual update, attention.py:527, 567, 572). With enough rows the bias and
+    the residual ride in the GEMM's epilogue; returns True then, False when the caller still has to add."""
+    if _rows(a) >= NATIVE_LINEAR_MIN_ROWS and linear_plain(lin) and _gemm_shape_ok(lin.weight) and x.is_contiguous() \
+            and _native.FEATURES["native_linears"]:
+        _native.linear(a, lin.weight, lin.bias, residual=x, out=x)
+        return True
+    return False
+
+
 def self_attention_fused(attn, x):
-    """to_out(attention(x Wq^T, x Wk^T, x Wv^T)) with one projection GEMM."""
+    """attention(x Wq^T, x Wk^T, x Wv^T) with one projection GEMM (before to_out)."""
     import comfy.ldm.modules.attention as ref
-    if not _attn_plain(attn) or attn.to_k.weight.shape != attn.to_q.weight.shape:
-        return attn(x)
     inner = attn.heads * attn.dim_head
-    qkv = torch.nn.functional.linear(x, _qkv_weight(attn))
-    out = ref.optimized_attention(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], attn.heads)
-    return attn.to_out(out)
+    qkv = project(x, _qkv_weight(attn), None, prefer_native=True)
+    return ref.optimized_attention(qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:], attn.heads)
 
 
 def _kv_key(attn, context):
@@ -76,15 +107,13 @@ def get_kv_cache(attn):
 
 
 def cross_attention_cached(attn, x, context):
+    """attention(x Wq^T, K(context), V(context)) with K / V cached per context tensor (before to_out)."""
     import comfy.ldm.modules.attention as ref
-    if not _attn_plain(attn):
-        return attn(x, context=context)
     key = _kv_key(attn, context)
     kv = attn.__dict__.get("_cgs_kv")
     if kv is None or kv[0] != key:
         kv = attn.__dict__["_cgs_kv"] = (key, attn.to_k(context), attn.to_v(context), context)
-    out = ref.optimized_attention(attn.to_q(x), kv[1], kv[2], attn.heads)
-    return attn.to_out(out)
+    return ref.optimized_attention(attn.to_q(x), kv[1], kv[2], attn.heads)
 
 
 def release_caches(module: torch.nn.Module) -> None:
@@ -107,7 +136,19 @@ def _block_fast_ok(blk, x, context, transformer_options) -> bool:
     for n in (blk.norm1, blk.norm2, blk.norm3):
         if n.comfy_cast_weights or n.weight is None or n.weight.dtype != layers.ACT_DTYPE:
             return False
-    return context is None or on_fast_device(context)
+    if not (_attn_plain(blk.attn1) and _attn_plain(blk.attn2) and blk.attn1.to_k.weight.shape == blk.attn1.to_q.weight.shape
+            and linear_plain(blk.attn1.to_out[0]) and linear_plain(blk.attn2.to_out[0])):
+        return False
+    return context is not None and on_fast_device(context)
+
+
+def _attend_add_norm(x, a, to_out, norm):
+    """x += to_out(a); return norm(x). Either the GEMM's epilogue does the add and a plain LayerNorm follows, or
+    cuBLASLt projects and the add rides in the LayerNorm kernel (cgs_add_layernorm_fwd)."""
+    lin = to_out[0]
+    if project_add_(x, a, lin):
+        return norm(x)
+    return _native.add_layer_norm_(x, to_out(a), norm.weight, norm.bias, norm.eps)
 
 
 def transformer_block_forward(self, x, context=None, transformer_options={}):
@@ -115,15 +156,14 @@ def transformer_block_forward(self, x, context=None, transformer_options={}):
         return ORIGINAL["BasicTransformerBlock._forward"](self, x, context, transformer_options)
     n = self.norm1(x)
     a = self_attention_fused(self.attn1, n)
-    n = _native.add_layer_norm_(x, a, self.norm2.weight, self.norm2.bias, self.norm2.eps)          # x += a
-    a = cross_attention_cached(self.attn2, n, context) if context is not None else self.attn2(n)
-    n = _native.add_layer_norm_(x, a, self.norm3.weight, self.norm3.bias, self.norm3.eps)          # x += a
+    n = _attend_add_norm(x, a, self.attn1.to_out, self.norm2)                                       # x += attn1(...)
+    a = cross_attention_cached(self.attn2, n, context)
+    n = _attend_add_norm(x, a, self.attn2.to_out, self.norm3)                                       # x += attn2(...)
     ff_in, ff_out = self.ff.net[0], self.ff.net[2]
-    if hasattr(ff_in, "proj") and linear_plain(ff_out) and ff_out.weight.shape[0] % 32 == 0 \
-            and ff_out.weight.shape[1] % 8 == 0:
-        # x = ff.net.2(geglu(n)) + x: bias and residual in the GEMM epilogue, written in place
-        return _native.linear(ff_in(n), ff_out.weight, ff_out.bias, residual=x, out=x)
-    h = self.ff(n)
+    h = ff_in(n)
+    if hasattr(ff_in, "proj") and project_add_(x, h, ff_out):
+        return x                                     # x += ff.net.2(geglu(n)): bias and residual in the GEMM epilogue
+    h = ff_out(self.ff.net[1](h))
     h += x
     return h
 

@@ -392,7 +392,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tc_fence_after();
             uint32_t sr[COLS];
 #pragma unroll
-            for (int c = 0; c < COLS; c += 32) tmem_ld_x32(s_addr + c, sr + c);
+            for (int c = 0; c + 32 <= COLS; c += 32) tmem_ld_x32(s_addr + c, sr + c);
+            if constexpr (COLS % 32 != 0) tmem_ld_x16(s_addr + (COLS / 32) * 32, sr + (COLS / 32) * 32);
             tmem_wait_ld();
             // S(j) is in registers: give the buffer back so S(j+1) is computed during this softmax
             tc_fence_before();
@@ -481,7 +482,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             mbar_wait(&o_full[t], (g - 1) & 1);
             tc_fence_after();
 #pragma unroll
-            for (int c = 0; c < COLS / 2; c += 32) tmem_st_x32(p_addr + c, pr + c);
+            for (int c = 0; c + 32 <= COLS / 2; c += 32) tmem_st_x32(p_addr + c, pr + c);
+            if constexpr ((COLS / 2) % 32 != 0) tmem_st_x16(p_addr + (COLS / 64) * 32, pr + (COLS / 64) * 32);
             if (__any_sync(0xffffffffu, need_rescale)) {
                 for (int c = 0; c < (dv_n >> 4); ++c) {
                     uint32_t orr[16];
@@ -650,13 +652,15 @@ static int attention_entry(const void* q, const void* k, const void* v, void* ou
     static const struct Knobs {
         long long* trace;
         int max_1cta;
-        bool no_3tile;
+        bool no_3tile, two_by_64, no_bn96;
         Knobs() {
             const char* e = getenv("CGS_ATTN_TRACE");
             trace = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr;
             e = getenv("CGS_ATTN_MAX_TILES_1CTA");
             max_1cta = e ? atoi(e) : 8;
             no_3tile = getenv("CGS_ATTN_NO_3TILE") != nullptr;
+            two_by_64 = getenv("CGS_ATTN_2X64") != nullptr;
+            no_bn96 = getenv("CGS_ATTN_NO_BN96") != nullptr;
         }
     } knobs;
     p.dbg = knobs.trace;
@@ -685,7 +689,12 @@ static int attention_entry(const void* q, const void* k, const void* v, void* ou
     const bool multi = Nq > attn::BLOCK_M && n_tiles > max_1cta && mask == nullptr;   // masked: one-tile variants only
     int nqt = 1, bn = 128;
     if (multi && d <= 64 && !knobs.no_3tile) { nqt = 3; bn = 64; }
+    else if (multi && d <= 64 && knobs.two_by_64) { nqt = 2; bn = 64; }
     else if (multi && 2 * (192 + dv_n) <= 512) { nqt = 2; }
+    // text cross-attention (77 keys, 154 when the prompts' lengths differ): 96-key tiles -- the softmax runs over
+    // every column of a tile, so a 128-column tile spends 40 % of its exponentials on padding
+    const bool short_keys = !multi && mask == nullptr && d <= 128 && Nk <= 192 && !knobs.no_bn96;
+    if (short_keys) bn = 96;
     int cols = 32;
     while (cols < nqt * (bn + bn / 2 + dv_n)) cols *= 2;
     p.tmem_cols = cols;
@@ -704,10 +713,13 @@ static int attention_entry(const void* q, const void* k, const void* v, void* ou
     }
     if (d <= 64) {
         if (nqt == 3) return launch_attn<1, 3, 4, 64>(tq, tk, tv, to, p, st);
+        if (nqt == 2 && bn == 64) return launch_attn<1, 2, 4, 64>(tq, tk, tv, to, p, st);
         if (nqt == 2) return launch_attn<1, 2, 3>(tq, tk, tv, to, p, st);
+        if (short_keys) return launch_attn<1, 1, 1, 96>(tq, tk, tv, to, p, st);
         return n_tiles > 2 ? launch_attn<1, 1, 2>(tq, tk, tv, to, p, st) : launch_attn<1, 1, 1>(tq, tk, tv, to, p, st);
     }
     if (d <= 128) {
+        if (short_keys) return launch_attn<2, 1, 1, 96>(tq, tk, tv, to, p, st);
         if (nqt == 2) return launch_attn<2, 2, 2>(tq, tk, tv, to, p, st);
         return n_tiles > 2 ? launch_attn<2, 1, 2>(tq, tk, tv, to, p, st) : launch_attn<2, 1, 1>(tq, tk, tv, to, p, st);
     }

@@ -34,6 +34,14 @@
 // the same 128 output columns side by side in TMEM. (With CTA pairs the leader stages the value rows and the peer
 // the gate rows.)
 //
+// Wave quantisation (EPI_LINEAR): the SDXL linears (M = 16384 / 65536, N = 1280 / 640) give 4.3 rounds of tiles, and
+// one image per GPU gives 80 tiles for 148 SMs. The tiles of the last, partly filled round are therefore dealt out
+// in 64-column pieces to ALL workers: a worker's piece is a narrower MMA (N = 64 .. 256) on the same A rows, an
+// independent set of output columns -- no reduction, no workspace, and every output element is still the same sum in
+// the same order, so results do not change. (Splitting those tiles along K instead -- partial accumulators through
+// global memory -- was built and measured first: 19 MB of fp32 partials per launch cost as much as the idle SMs.)
+// The same mechanism serves the last column of tiles when N is not a multiple of 256 (N = 640: an N = 128 MMA).
+//
 // Tensor-core bound. Algorithmic FLOPs = 2 * M * K * (2N) for GEGLU, 2 * M * K * N for linear.
 #include "common.cuh"
 
@@ -92,6 +100,66 @@ __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int
     mb = g * gemm::GROUP_M + (r - nb * gm);
 }
 
+// One unit of work of a persistent worker: `width` output columns of one tile, starting `n_off` columns into it
+// (a whole tile: n_off 0, width = what the tile has of N).
+struct Piece {
+    int tile;
+    int n_off;
+    int width;      // multiple of 32; 0 = nothing to do (all roles skip it)
+};
+
+// Full rounds: worker w takes tiles w, w + W, ... whole. Last, partly filled round (rem < W tiles), EPI_LINEAR only:
+// its rem * 4 column groups (64 columns each) are dealt out contiguously and evenly to all workers, so a worker gets
+// the end of one tile and / or the beginning of the next.
+template <int EPI>
+struct Schedule {
+    int workers, num_tiles, tiles_m, tiles_n, N, full_rounds, rem, active, groups;
+    __device__ Schedule(int workers_, int tiles_m_, int tiles_n_, int N_)
+        : workers(workers_), num_tiles(tiles_m_ * tiles_n_), tiles_m(tiles_m_), tiles_n(tiles_n_), N(N_) {
+        full_rounds = num_tiles / workers;
+        rem = num_tiles - full_rounds * workers;
+        groups = rem * 4;
+        active = (EPI == gemm::EPI_LINEAR) ? (groups < workers ? groups : workers) : rem;
+    }
+    __device__ int tile_width(int tile) const {
+        if (EPI == gemm::EPI_GEGLU) return gemm::UMMA_N;
+        int mb, nb;
+        tile_coords(tile, tiles_m, tiles_n, mb, nb);
+        const int left = N - nb * gemm::UMMA_N;
+        return left < gemm::UMMA_N ? left : gemm::UMMA_N;
+    }
+    __device__ int items(int w) const {
+        if (w >= active) return full_rounds;
+        if (EPI == gemm::EPI_GEGLU) return full_rounds + 1;
+        const int a = (int)((long long)groups * w / active), b = (int)((long long)groups * (w + 1) / active);
+        return full_rounds + ((b - 1) / 4 - a / 4) + 1;
+    }
+    __device__ Piece item(int w, int i) const {
+        Piece p;
+        p.n_off = 0;
+        if (i < full_rounds) {
+            p.tile = w + i * workers;
+            p.width = tile_width(p.tile);
+            return p;
+        }
+        if (EPI == gemm::EPI_GEGLU) {
+            p.tile = full_rounds * workers + w;
+            p.width = gemm::UMMA_N;
+            return p;
+        }
+        const int a = (int)((long long)groups * w / active), b = (int)((long long)groups * (w + 1) / active);
+        const int slot = a / 4 + (i - full_rounds);
+        const int g0 = (a > slot * 4 ? a : slot * 4) - slot * 4;
+        const int g1 = (b < slot * 4 + 4 ? b : slot * 4 + 4) - slot * 4;
+        p.tile = full_rounds * workers + slot;
+        p.n_off = g0 * 64;
+        const int have = tile_width(p.tile) - p.n_off;
+        p.width = (g1 - g0) * 64 < have ? (g1 - g0) * 64 : have;
+        if (p.width < 0) p.width = 0;
+        return p;
+    }
+};
+
 struct alignas(16) BF8 {
     __nv_bfloat162 v[4];
 };
@@ -125,8 +193,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int workers = PAIR ? (gridDim.x >> 1) : gridDim.x;
     const int tiles_m = (M + C::TILE_M - 1) / C::TILE_M;
     const int tiles_n = (EPI == EPI_GEGLU) ? (N / BN_HALF) : ((N + UMMA_N - 1) / UMMA_N);
-    const int num_tiles = tiles_m * tiles_n;
     const int kblocks = (K + BK - 1) / BK;
+    const Schedule<EPI> sched(workers, tiles_m, tiles_n, N);
+    const int n_items = sched.items(worker);
 
     if (warp == 0 && elect_one()) {
         tma_prefetch_desc(&tmA);
@@ -164,12 +233,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = worker; t < num_tiles; t += workers) {
+            for (int i = 0; i < n_items; ++i) {
+                const Piece pc = sched.item(worker, i);
+                if (pc.width <= 0) continue;
                 int mb, nb;
-                tile_coords(t, tiles_m, tiles_n, mb, nb);
+                tile_coords(pc.tile, tiles_m, tiles_n, mb, nb);
                 const int m0 = mb * C::TILE_M + (int)rank * BM;
-                const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N;
-                const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : nb * UMMA_N + BN_HALF;
+                // B rows of this piece. GEGLU: value rows + gate rows of the tile's 128 output columns. Linear: `width`
+                // consecutive rows of W; with CTA pairs each CTA stages half of them (a full 128-row box is loaded,
+                // the MMA reads the first width / 2 rows of it).
+                const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N + pc.n_off;
+                const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : row0 + (PAIR ? pc.width / 2 : BN_HALF);
+                const bool two_boxes = PAIR || pc.width > BN_HALF;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
@@ -180,14 +255,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                         tma_load_2d_pair(sa, &tmA, &full[stage], kb * BK, m0);
                         tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, rank == 0 ? row0 : row1);
                     } else {
-                        mbar_expect_tx(&full[stage], STAGE_BYTES);
+                        mbar_expect_tx(&full[stage], two_boxes ? STAGE_BYTES : A_BYTES + BN_HALF * BK * 2);
                         tma_load_2d(sa, &tmA, &full[stage], kb * BK, m0);
                         if (dbg & 4) {   // experiment: reload the A box instead of B (1/3 of the distinct L2 lines)
                             tma_load_2d(sb, &tmA, &full[stage], kb * BK, m0);
                             tma_load_2d(sb + BN_HALF * BK * 2, &tmA, &full[stage], kb * BK, m0);
                         } else {
                             tma_load_2d(sb, &tmB, &full[stage], kb * BK, row0);
-                            tma_load_2d(sb + BN_HALF * BK * 2, &tmB, &full[stage], kb * BK, row1);
+                            if (two_boxes) tma_load_2d(sb + BN_HALF * BK * 2, &tmB, &full[stage], kb * BK, row1);
                         }
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -198,12 +273,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     } else if (warp == 1) {
         // ------------------------------ MMA issuer (leader CTA only for pairs) ------
         if (rank == 0 && elect_one()) {
-            const uint32_t idesc = umma_idesc_bf16(C::TILE_M, UMMA_N, 0);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int t = worker; t < num_tiles; t += workers) {
+            for (int i = 0; i < n_items; ++i) {
+                const Piece pc = sched.item(worker, i);
+                if (pc.width <= 0) continue;
+                const uint32_t idesc = umma_idesc_bf16(C::TILE_M, pc.width, 0);
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * UMMA_N;
@@ -252,15 +329,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         };
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int t = worker; t < num_tiles; t += workers) {
+        for (int i = 0; i < n_items; ++i) {
+            const Piece pc = sched.item(worker, i);
+            if (pc.width <= 0) continue;
             int mb, nb;
-            tile_coords(t, tiles_m, tiles_n, mb, nb);
+            tile_coords(pc.tile, tiles_m, tiles_n, mb, nb);
             const int row_base = mb * C::TILE_M + (int)rank * BM;
             const int row = row_base + row_in_tile;
+            const int col_base = nb * UMMA_N + pc.n_off;        // (EPI_LINEAR) first output column of this piece
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * UMMA_N + (static_cast<uint32_t>(quad * 32) << 16);
-            constexpr int PASSES = (EPI == EPI_GEGLU) ? 1 : 2;
+            const int PASSES = (EPI == EPI_GEGLU) ? 1 : (pc.width > 128 ? 2 : 1);
 #pragma unroll 1
             for (int pass = 0; pass < PASSES; ++pass) {
                 BF8 o[4];
@@ -297,12 +377,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                         }
                     }
                 } else {
-                    col = nb * UMMA_N + pass * 128 + cg * 32;
+                    col = col_base + pass * 128 + cg * 32;
                     uint32_t v[32];
                     tmem_ld_x32(taddr + pass * 128 + cg * 32, v);
                     tmem_wait_ld();
                     if (pass == PASSES - 1) release_acc(acc);
-                    const bool col_ok = col < N;      // N % 32 == 0: a 32-column group is all in or all out
+                    // widths are multiples of 32: a 32-column group is all in or all out of the piece
+                    const bool col_ok = pass * 128 + cg * 32 < pc.width;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         BF8 bv, rv;
@@ -335,9 +416,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 fence_proxy_async_smem();
                 named_bar_sync(1, EPI_THREADS);
                 if (store_leader && !(dbg & 2) && row_base < M) {
-                    const int c0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N + pass * 128;
-                    if (c0 < N) tma_store_2d(&tmO, out_stage, c0, row_base);
-                    if (c0 + 64 < N) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, row_base);
+                    // 64-column boxes; pieces are multiples of 64 columns except at the edge of N, where the tensor map clips
+                    const int c0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : col_base + pass * 128;
+                    const int left = (EPI == EPI_GEGLU) ? BN_HALF : pc.width - pass * 128;
+                    if (left > 0) tma_store_2d(&tmO, out_stage, c0, row_base);
+                    if (left > 64) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, row_base);
                     tma_store_commit();
                 }
             }
@@ -365,8 +448,10 @@ static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     const int sms = sm_count();
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
+    // EPI_LINEAR deals the last round out in 64-column pieces: up to 4 workers per tile can be put to use
+    const long long useful = (EPI == EPI_LINEAR) ? tiles * 4 : tiles;
     if (PAIR) {
-        const long long pairs = tiles < sms / 2 ? tiles : sms / 2;
+        const long long pairs = useful < sms / 2 ? useful : sms / 2;
         cfg.gridDim = dim3((unsigned)(2 * pairs));
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2;
@@ -375,7 +460,7 @@ static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
         cfg.attrs = attr;
         cfg.numAttrs = 1;
     } else {
-        cfg.gridDim = dim3((unsigned)(tiles < sms ? tiles : sms));
+        cfg.gridDim = dim3((unsigned)(useful < sms ? useful : sms));
     }
     cfg.blockDim = dim3(THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
@@ -446,10 +531,11 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
     const int tiles_n = (epi == EPI_GEGLU) ? N / BN_HALF : (N + UMMA_N - 1) / UMMA_N;
     const long long tiles1 = ((M + BM - 1) / BM) * tiles_n;
     const long long tiles2 = ((M + 2 * BM - 1) / (2 * BM)) * tiles_n;
-    // CTA pairs need enough M256 tiles to keep the 74 pairs busy for a few rounds; below that the M128 tiling has
-    // twice the parallelism
-    const int pairs = sm_count() / 2;
-    bool pair = tiles2 >= 3LL * pairs;
+    // CTA pairs pay off when the mainloop is long enough to be bound by the operand feed: measured on the SDXL shapes
+    // (profiles/r02_kernel_bench.json), K >= 1024 wins 7-15 % with pairs at every M, K = 640 loses 3-14 % (ten k-blocks
+    // per tile: the epilogue hand-over between two SMs is a visible part of every tile)
+    (void)tiles2;
+    bool pair = K >= 1024;
     if (g_gemm_force_variant == 1) pair = false;
     if (g_gemm_force_variant == 2) pair = true;
     auto bp = static_cast<const __nv_bfloat16*>(bias);

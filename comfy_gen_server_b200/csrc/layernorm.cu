@@ -117,6 +117,86 @@ layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
     }
 }
 
+// Plain LayerNorm at the UNet's real sizes is a SMALL kernel (SDXL level 2: 84 MB, 13 us at the HBM roofline): with
+// one row per warp and one-shot CTAs a quarter of the time went into launch ramp, wave quantisation (3.5 waves) and
+// the serial load -> reduce -> reduce -> store chain of each warp (0.44-0.53 of the measured copy bandwidth). Here
+// the CTAs are persistent (4 per SM), every warp walks rows with a grid stride and the NEXT row's 16-byte loads are
+// issued before the reductions of the current one, so each warp always has a row in flight.
+template <int MAXV>
+__global__ void __launch_bounds__(256, (MAXV <= 5 ? 4 : 2))
+layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
+                        const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y, long long rows, int C,
+                        float eps) {
+    const int lane = threadIdx.x & 31;
+    const long long stride = (long long)gridDim.x * (blockDim.x >> 5);
+    long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nvec = C >> 3;
+    const Vec8* g8 = reinterpret_cast<const Vec8*>(gamma);       // (re-read per row: 2.5 KB each, L1 hits)
+    const Vec8* b8 = reinterpret_cast<const Vec8*>(beta);
+    Vec8 nxt[MAXV];
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i)
+        if (lane + i * 32 < nvec) nxt[i] = ld_stream(reinterpret_cast<const Vec8*>(x + row * C) + lane + i * 32);
+    while (row < rows) {
+        Vec8 a[MAXV];
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) a[i] = nxt[i];
+        const long long next = row + stride;
+        if (next < rows) {
+#pragma unroll
+            for (int i = 0; i < MAXV; ++i)
+                if (lane + i * 32 < nvec) nxt[i] = ld_stream(reinterpret_cast<const Vec8*>(x + next * C) + lane + i * 32);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) {
+            if (lane + i * 32 < nvec) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 t = __bfloat1622float2(a[i].v[j]);
+                    sum += t.x + t.y;
+                }
+            }
+        }
+        const float mean = warp_sum(sum) / (float)C;          // (same arithmetic as layernorm_kernel: bit-equal results)
+        float sq = 0.f;
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) {
+            if (lane + i * 32 < nvec) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 t = __bfloat1622float2(a[i].v[j]);
+                    const float d0 = t.x - mean, d1 = t.y - mean;
+                    sq += d0 * d0 + d1 * d1;
+                }
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+        Vec8* yr = reinterpret_cast<Vec8*>(y + row * C);
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) {
+            const int v = lane + i * 32;
+            if (v < nvec) {
+                const Vec8 g = g8[v];
+                const Vec8 b = b8[v];
+                Vec8 o;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 t = __bfloat1622float2(a[i].v[j]);
+                    const float2 gg = __bfloat1622float2(g.v[j]);
+                    const float2 bb = __bfloat1622float2(b.v[j]);
+                    const float o0 = (t.x - mean) * rstd * gg.x + bb.x;
+                    const float o1 = (t.y - mean) * rstd * gg.y + bb.y;
+                    o.v[j] = __floats2bfloat162_rn(o0, o1);
+                }
+                yr[v] = o;
+            }
+        }
+        row = next;
+    }
+}
+
 template <bool ADD>
 static int launch_ln(const void* x, const void* res, const void* gamma, const void* beta,
                      void* x_out, void* y, long long rows, int C, float eps, cudaStream_t stream) {
@@ -137,6 +217,19 @@ static int launch_ln(const void* x, const void* res, const void* gamma, const vo
     auto bp = static_cast<const __nv_bfloat16*>(beta);
     auto xo = static_cast<__nv_bfloat16*>(x_out);
     auto yp = static_cast<__nv_bfloat16*>(y);
+    if (!ADD && C <= 1280) {
+        // persistent streaming variant (see layernorm_stream_kernel)
+        const long long resident = (long long)sm_count() * 4;
+        const unsigned pgrid = (unsigned)(grid < resident ? grid : resident);
+        if (C <= 512)
+            layernorm_stream_kernel<2><<<pgrid, warps * 32, 0, stream>>>(xp, gp, bp, yp, rows, C, eps);
+        else if (C <= 768)
+            layernorm_stream_kernel<3><<<pgrid, warps * 32, 0, stream>>>(xp, gp, bp, yp, rows, C, eps);
+        else
+            layernorm_stream_kernel<5><<<pgrid, warps * 32, 0, stream>>>(xp, gp, bp, yp, rows, C, eps);
+        CGS_CUDA_CHECK(cudaGetLastError());
+        return kOk;
+    }
     if (C <= 512)
         layernorm_kernel<2, ADD><<<grid, warps * 32, 0, stream>>>(xp, rp, gp, bp, xo, yp, rows, C, eps);
     else if (C <= 768)

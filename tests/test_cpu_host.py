@@ -191,6 +191,27 @@ def test_drop_in_reproduces_reference_latents_with_torch_stand_ins(reference_tre
     assert (out - g["final"]).abs().max() < 2e-3 and cosine(out, g["final"]) > 0.999999
 
 
+def test_drop_in_with_every_linear_on_the_library_gemm(reference_tree):
+    """The large-batch routing of the transformer block (fused QKV, to_out + residual and ff.net.2 + residual on the
+    library GEMM, plain LayerNorm after them) forced on for the tiny model: same latents as the reference's golden."""
+    import comfy.sample
+    import fake_native
+    from comfy_gen_server_b200 import block, integration
+    g, seed, patcher, latent, noise, pos, neg = _cpu_case("tiny_sdxl", "e2e_tiny_sdxl_dpmpp2m", 16)
+    saved = block.NATIVE_LINEAR_MIN_ROWS
+    with fake_native.patched() as calls, torch.inference_mode():
+        integration.install()
+        block.NATIVE_LINEAR_MIN_ROWS = 0
+        try:
+            out = comfy.sample.sample(patcher, noise, 30, 7.0, "dpmpp_2m", "karras", pos, neg, latent, seed=seed,
+                                      disable_pbar=True)
+        finally:
+            block.NATIVE_LINEAR_MIN_ROWS = saved
+            integration.uninstall()
+    assert calls.get("add_layer_norm_", 0) == 0 and calls["linear"] > 0 and calls["layer_norm"] > 0
+    assert (out - g["final"]).abs().max() < 2e-3 and cosine(out, g["final"]) > 0.999999
+
+
 def test_hooks_and_non_plain_conds_fall_through_to_the_reference_composition(reference_tree):
     """(i) a post-CFG hook, (ii) an attention output patch, (iii) two positive conds with an area and a strength: the
     fused step / fused block must stand aside for EVERY step and the result must equal the unmodified reference's."""

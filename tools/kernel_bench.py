@@ -39,7 +39,10 @@ def timeit(fn, iters=10, warmup=3, flush=True):
     times = []
     for _ in range(iters):
         if flush:
-            _flush.zero_()
+            # evict the L2 with CLEAN lines (a read pass over 256 MiB): zeroing the buffer instead leaves 126 MB of
+            # dirty lines whose write-back is then charged to the kernel under test (it halved the bandwidth of the
+            # 84 MB LayerNorm launches in round 1's numbers)
+            _flush.sum()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         fn()
@@ -96,6 +99,35 @@ def bench_gemm_variants():
         for v, name in ((1, "single_cta"), (2, "cta_pair"), (0, "auto")):
             lib.cgs_gemm_set_variant(v)
             row[name + "_tflops"] = flops / timeit(fn) / 1e9
+        lib.cgs_gemm_set_variant(0)
+        out.append(row)
+    return out
+
+
+def bench_gemm_variants():
+    """one CTA per tile vs CTA pairs (cgs_gemm_set_variant) vs cuBLASLt, on the SDXL GEMM shapes"""
+    out = []
+    lib = N.load_library()
+    shapes = [("geglu", "sdxl_L2", 16 * 1024, 1280, 5120), ("geglu", "sdxl_L1", 16 * 4096, 640, 2560),
+              ("linear", "sdxl_L2_ff_out", 16 * 1024, 5120, 1280), ("linear", "sdxl_L1_ff_out", 16 * 4096, 2560, 640),
+              ("linear", "sdxl_L2_to_q", 16 * 1024, 1280, 1280), ("linear", "sdxl_L1_to_q", 16 * 4096, 640, 640),
+              ("linear", "sdxl_L2_qkv", 16 * 1024, 1280, 3840), ("linear", "sdxl_L1_qkv", 16 * 4096, 640, 1920),
+              ("linear", "sdxl_L2_ff_out_b1", 2 * 1024, 5120, 1280), ("linear", "sdxl_L2_to_q_b1", 2 * 1024, 1280, 1280),
+              ("linear", "sdxl_L2_qkv_b1", 2 * 1024, 1280, 3840), ("geglu", "sdxl_L2_b1", 2 * 1024, 1280, 5120)]
+    for kind, label, M, K, Nn in shapes:
+        row = {"kernel": "gemm_variants", "kind": kind, "case": label, "M": M, "K": K, "N": Nn}
+        if kind == "geglu":
+            x, w, b = rnd((M, K)), rnd((2 * Nn, K), scale=K ** -0.5), rnd((2 * Nn,), scale=0.1)
+            fn = lambda: N.geglu(x, w, b)
+            flops = 2.0 * M * K * 2 * Nn
+        else:
+            x, w, b = rnd((M, K)), rnd((Nn, K), scale=K ** -0.5), rnd((Nn,), scale=0.1)
+            fn = lambda: N.linear(x, w, b)
+            flops = 2.0 * M * K * Nn
+            row["cublaslt_tflops"] = round(flops / timeit(lambda: torch.nn.functional.linear(x, w, b)) / 1e9, 1)
+        for v, name in ((1, "single_cta"), (2, "cta_pair"), (0, "auto")):
+            lib.cgs_gemm_set_variant(v)
+            row[name + "_tflops"] = round(flops / timeit(fn) / 1e9, 1)
         lib.cgs_gemm_set_variant(0)
         out.append(row)
     return out
