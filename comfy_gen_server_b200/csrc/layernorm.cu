@@ -117,80 +117,115 @@ layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
     }
 }
 
-// Plain LayerNorm at the UNet's real sizes is a SMALL kernel (SDXL level 2: 84 MB, 13 us at the HBM roofline): with
-// one row per warp and one-shot CTAs a quarter of the time went into launch ramp, wave quantisation (3.5 waves) and
-// the serial load -> reduce -> reduce -> store chain of each warp (0.44-0.53 of the measured copy bandwidth). Here
-// the CTAs are persistent (4 per SM), every warp walks rows with a grid stride and the NEXT row's 16-byte loads are
-// issued before the reductions of the current one, so each warp always has a row in flight.
+// Plain LayerNorm, the form every block of the large-batch path uses now that the residual adds ride in the GEMM
+// epilogues. The one-row-per-warp kernel above reached only 0.40-0.45 of the measured copy bandwidth at the UNet's
+// sizes -- and a persistent, prefetching version of it gained nothing: it is ISSUE-bound, not memory-bound
+// (~15 scalar instructions per element: the bf16 pairs are unpacked three times, the statistics and the affine
+// transform run one lane-element at a time). This kernel
+//   * unpacks a row's bf16 pairs ONCE into packed fp32x2 registers,
+//   * runs every pass on the packed FADD2 / FFMA2 pipe: sum, (x - mean)^2, and y = x * (rstd * gamma) + (beta -
+//     mean * rstd * gamma) -- 4.5 instructions per element,
+//   * keeps gamma / beta as fp32 in shared memory (conflict-free float4 arrays), filled once per CTA,
+//   * is persistent (3 CTAs per SM) with the NEXT row's 16-byte loads issued before the current row's reductions.
 template <int MAXV>
-__global__ void __launch_bounds__(256, (MAXV <= 5 ? 4 : 2))
+__global__ void __launch_bounds__(256, 3)
 layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
                         const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y, long long rows, int C,
                         float eps) {
+    extern __shared__ float4 gb_smem[];                 // [4][nvec]: gamma lo / hi halves, beta lo / hi halves
     const int lane = threadIdx.x & 31;
+    const int nvec = C >> 3;
+    float4* g_lo = gb_smem;
+    float4* g_hi = g_lo + nvec;
+    float4* b_lo = g_hi + nvec;
+    float4* b_hi = b_lo + nvec;
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+        const Vec8 g = reinterpret_cast<const Vec8*>(gamma)[v];
+        const Vec8 b = reinterpret_cast<const Vec8*>(beta)[v];
+        const float2 g0 = __bfloat1622float2(g.v[0]), g1 = __bfloat1622float2(g.v[1]);
+        const float2 g2 = __bfloat1622float2(g.v[2]), g3 = __bfloat1622float2(g.v[3]);
+        const float2 b0 = __bfloat1622float2(b.v[0]), b1 = __bfloat1622float2(b.v[1]);
+        const float2 b2 = __bfloat1622float2(b.v[2]), b3 = __bfloat1622float2(b.v[3]);
+        g_lo[v] = make_float4(g0.x, g0.y, g1.x, g1.y);
+        g_hi[v] = make_float4(g2.x, g2.y, g3.x, g3.y);
+        b_lo[v] = make_float4(b0.x, b0.y, b1.x, b1.y);
+        b_hi[v] = make_float4(b2.x, b2.y, b3.x, b3.y);
+    }
+    __syncthreads();
     const long long stride = (long long)gridDim.x * (blockDim.x >> 5);
     long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
-    const int nvec = C >> 3;
-    const Vec8* g8 = reinterpret_cast<const Vec8*>(gamma);       // (re-read per row: 2.5 KB each, L1 hits)
-    const Vec8* b8 = reinterpret_cast<const Vec8*>(beta);
     Vec8 nxt[MAXV];
 #pragma unroll
     for (int i = 0; i < MAXV; ++i)
         if (lane + i * 32 < nvec) nxt[i] = ld_stream(reinterpret_cast<const Vec8*>(x + row * C) + lane + i * 32);
+    const float inv_c = 1.0f / (float)C;
     while (row < rows) {
-        Vec8 a[MAXV];
+        // bf16 pair -> packed fp32 pair: the low half shifted up, the high half masked
+        uint64_t a[MAXV][4];
 #pragma unroll
-        for (int i = 0; i < MAXV; ++i) a[i] = nxt[i];
+        for (int i = 0; i < MAXV; ++i) {
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(&nxt[i]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a[i][j] = pack_u32x2(w[j] << 16, w[j] & 0xffff0000u);
+        }
         const long long next = row + stride;
         if (next < rows) {
 #pragma unroll
             for (int i = 0; i < MAXV; ++i)
                 if (lane + i * 32 < nvec) nxt[i] = ld_stream(reinterpret_cast<const Vec8*>(x + next * C) + lane + i * 32);
         }
-        float sum = 0.f;
+        uint64_t s2 = 0ull;
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) {
+            if (lane + i * 32 < nvec) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) s2 = fadd2(s2, a[i][j]);
+            }
+        }
+        float s_lo, s_hi;
+        unpack_f32x2(s2, s_lo, s_hi);
+        const float mean = warp_sum(s_lo + s_hi) * inv_c;
+        const uint64_t negmean2 = pack_f32x2(-mean, -mean);
+        uint64_t q2 = 0ull;
 #pragma unroll
         for (int i = 0; i < MAXV; ++i) {
             if (lane + i * 32 < nvec) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const float2 t = __bfloat1622float2(a[i].v[j]);
-                    sum += t.x + t.y;
+                    const uint64_t d2 = fadd2(a[i][j], negmean2);
+                    q2 = ffma2(d2, d2, q2);
                 }
             }
         }
-        const float mean = warp_sum(sum) / (float)C;          // (same arithmetic as layernorm_kernel: bit-equal results)
-        float sq = 0.f;
-#pragma unroll
-        for (int i = 0; i < MAXV; ++i) {
-            if (lane + i * 32 < nvec) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 t = __bfloat1622float2(a[i].v[j]);
-                    const float d0 = t.x - mean, d1 = t.y - mean;
-                    sq += d0 * d0 + d1 * d1;
-                }
-            }
-        }
-        const float rstd = rsqrtf(warp_sum(sq) / (float)C + eps);
+        float q_lo, q_hi;
+        unpack_f32x2(q2, q_lo, q_hi);
+        const float rstd = rsqrtf(warp_sum(q_lo + q_hi) * inv_c + eps);
+        const uint64_t rstd2 = pack_f32x2(rstd, rstd);
         Vec8* yr = reinterpret_cast<Vec8*>(y + row * C);
 #pragma unroll
         for (int i = 0; i < MAXV; ++i) {
             const int v = lane + i * 32;
             if (v < nvec) {
-                const Vec8 g = g8[v];
-                const Vec8 b = b8[v];
-                Vec8 o;
+                const float4 gl = g_lo[v], gh = g_hi[v], bl = b_lo[v], bh = b_hi[v];
+                const uint64_t g2[4] = {pack_f32x2(gl.x, gl.y), pack_f32x2(gl.z, gl.w), pack_f32x2(gh.x, gh.y),
+                                        pack_f32x2(gh.z, gh.w)};
+                const uint64_t b2[4] = {pack_f32x2(bl.x, bl.y), pack_f32x2(bl.z, bl.w), pack_f32x2(bh.x, bh.y),
+                                        pack_f32x2(bh.z, bh.w)};
+                uint32_t o[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const float2 t = __bfloat1622float2(a[i].v[j]);
-                    const float2 gg = __bfloat1622float2(g.v[j]);
-                    const float2 bb = __bfloat1622float2(b.v[j]);
-                    const float o0 = (t.x - mean) * rstd * gg.x + bb.x;
-                    const float o1 = (t.y - mean) * rstd * gg.y + bb.y;
-                    o.v[j] = __floats2bfloat162_rn(o0, o1);
+                    const uint64_t gs = ffma2(g2[j], rstd2, 0ull);             // rstd * gamma
+                    const uint64_t bs = ffma2(negmean2, gs, b2[j]);            // beta - mean * rstd * gamma
+                    const uint64_t y2 = ffma2(a[i][j], gs, bs);
+                    float lo, hi;
+                    unpack_f32x2(y2, lo, hi);
+                    o[j] = pack_bf16x2(lo, hi);
                 }
-                yr[v] = o;
+                Vec8 ov;
+                uint32_t* ow = reinterpret_cast<uint32_t*>(&ov);
+                ow[0] = o[0]; ow[1] = o[1]; ow[2] = o[2]; ow[3] = o[3];
+                yr[v] = ov;
             }
         }
         row = next;
@@ -218,15 +253,16 @@ static int launch_ln(const void* x, const void* res, const void* gamma, const vo
     auto xo = static_cast<__nv_bfloat16*>(x_out);
     auto yp = static_cast<__nv_bfloat16*>(y);
     if (!ADD && C <= 1280) {
-        // persistent streaming variant (see layernorm_stream_kernel)
-        const long long resident = (long long)sm_count() * 4;
+        // packed-math persistent variant (see layernorm_stream_kernel)
+        const long long resident = (long long)sm_count() * 3;
         const unsigned pgrid = (unsigned)(grid < resident ? grid : resident);
+        const size_t smem = (size_t)(C >> 3) * 4 * sizeof(float4);
         if (C <= 512)
-            layernorm_stream_kernel<2><<<pgrid, warps * 32, 0, stream>>>(xp, gp, bp, yp, rows, C, eps);
+            layernorm_stream_kernel<2><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, rows, C, eps);
         else if (C <= 768)
-            layernorm_stream_kernel<3><<<pgrid, warps * 32, 0, stream>>>(xp, gp, bp, yp, rows, C, eps);
+            layernorm_stream_kernel<3><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, rows, C, eps);
         else
-            layernorm_stream_kernel<5><<<pgrid, warps * 32, 0, stream>>>(xp, gp, bp, yp, rows, C, eps);
+            layernorm_stream_kernel<5><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, rows, C, eps);
         CGS_CUDA_CHECK(cudaGetLastError());
         return kOk;
     }
