@@ -265,6 +265,9 @@ def run_ours(args):
                             f"same schedule, batch and inputs, CUDA events around the call (incl. its per-step syncs)"}
 
     integration.install()
+    if args.native is not None:         # A/B: which of the block's projections run on the library GEMM
+        for f in ("qkv", "to_out", "ff_out"):
+            _native.FEATURES["native_" + f] = f in args.native.split(",")
 
     # ---- device-resident leg: K denoise steps through the fused step of the drop-in --------------
     guider = comfy.samplers.CFGGuider(patcher)
@@ -351,6 +354,7 @@ def run_ours(args):
         attn_ms, attn_flops, attn_n = family_pass("attention", attn_steps)
         ln_ms, ln_bytes, ln_n = family_pass("add_layernorm", min(args.steps, 3))
         pln_ms, pln_bytes, pln_n = family_pass("layernorm", min(args.steps, 3))
+        lin_ms, lin_flops, lin_n = family_pass("linear", min(args.steps, 3))
 
         # ---- end-to-end leg: public API, pinned host buffers -> final latents on the host -------
         noise_h, latent_h = noise.pin_memory(), latent.pin_memory()
@@ -429,6 +433,11 @@ def run_ours(args):
                                        "achieved": lnbw, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                        "frac": lnbw / peaks["hbm_gbs"], "launches_timed": ln_n,
                                        "ms_in_kernel_per_step": ln_ms / min(args.steps, 3)},
+            "roofline_linear": {"kernel": "gemm_kernel<EPI_LINEAR> (cgs_linear_fwd: fused QKV, to_out / ff.net.2 + residual)",
+                                "bound": "tensor", "achieved": lin_flops / (lin_ms * 1e-3) / 1e12 if lin_ms > 0 else 0.0,
+                                "peak": peak_tf, "unit": "TFLOP/s", "launches_timed": lin_n,
+                                "frac": (lin_flops / (lin_ms * 1e-3) / 1e12 / peak_tf) if lin_ms > 0 else 0.0,
+                                "ms_in_kernel_per_step": lin_ms / min(args.steps, 3)},
             "roofline_layernorm": {"kernel": "layernorm_stream_kernel (cgs_layernorm_fwd)", "bound": "hbm",
                                    "achieved": plnbw, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                    "frac": plnbw / peaks["hbm_gbs"], "launches_timed": pln_n,
@@ -470,6 +479,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-library-baseline", action="store_true")
+    ap.add_argument("--native", default=None, help="A/B: comma list of qkv,to_out,ff_out on the library GEMM")
     ap.add_argument("--profile", action="store_true",
                     help="only the timed denoise steps, bracketed by cudaProfilerStart/Stop (for ncu)")
     args = ap.parse_args()

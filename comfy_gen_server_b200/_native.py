@@ -317,7 +317,10 @@ def _group_norm_nhwc(x, weight, bias, groups, eps, silu, add_nc):
 # Switches for tools/ablation.py: each one sends an op back to the library call it replaced, so that the step-time value
 # of a kernel can be measured inside one process on one GPU (box-to-box variation is larger than most of them).
 FEATURES = {"residual_add": True, "cat_channels": True, "upsample2x": True, "fold_conv_bias": True,
-            "native_linears": True}
+            # which Linear layers of the transformer block run on this library's GEMM (block.py): measured in-step on
+            # SDXL 1024^2 batch 8 (profiles/r02_linear_routing.json): to_out + ff.net.2 with the residual add in the
+            # epilogue 111.5 ms / step, nothing 112.5, all three 112.0, ff.net.2 alone 113.4
+            "native_qkv": False, "native_to_out": True, "native_ff_out": True}
 
 
 def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:

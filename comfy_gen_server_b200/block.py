@@ -50,11 +50,15 @@ def _qkv_weight(attn):
     return attn.__dict__["_cgs_qkv_w"]
 
 
-# Which Linear layers of the fast path run on the tcgen05 GEMM of this library and which stay on cuBLASLt, by measurement
-# on the SDXL shapes (profiles/r02_kernel_bench.json): with CTA pairs (K >= 1024) the GEMM is 7 % ahead of cuBLASLt on
-# the fused QKV projection; on the square projections it is 10-15 % behind, which the epilogue more than pays back
-# where it fuses the block's residual add (`x += n` disappears from the LayerNorm that follows). Below ~8 k rows (one or
-# two images per GPU) there are too few tiles for 148 SMs and cuBLASLt's split-K kernels win by up to 2x.
+# Which Linear layers of the fast path run on the tcgen05 GEMM of this library and which stay on cuBLASLt is decided by
+# measurement (profiles/r02_kernel_bench.json, profiles/r02_linear_routing.json; switches in _native.FEATURES):
+#   * to_out and ff.net.2 take the library GEMM because its epilogue fuses bias AND the block's residual add (`x += n`
+#     leaves the LayerNorm that follows); stand-alone the GEMM is 8-12 % behind cuBLASLt on these shapes, in the step
+#     the fusion wins 1 ms of 112;
+#   * the fused QKV projection is 2-7 % ahead of cuBLASLt stand-alone (CTA pairs) but not inside the power-capped
+#     step: it stays on cuBLASLt, as do to_q and the K / V projections of the text context (once per schedule);
+#   * below ~8 k rows (one or two images per GPU) there are too few tiles for 148 SMs and cuBLASLt's split-K kernels
+#     win by up to 2x: everything stays on cuBLASLt there.
 NATIVE_LINEAR_MIN_ROWS = 8192
 
 
@@ -69,16 +73,16 @@ def _gemm_shape_ok(weight) -> bool:
 def project(x, weight, bias=None, prefer_native=False):
     """x W^T (+ bias): the library GEMM where it is the faster one (see above), cuBLASLt otherwise."""
     if prefer_native and _rows(x) >= NATIVE_LINEAR_MIN_ROWS and weight.shape[1] >= 1024 and _gemm_shape_ok(weight) \
-            and _native.FEATURES["native_linears"]:
+            and _native.FEATURES["native_qkv"]:
         return _native.linear(x, weight, bias)
     return torch.nn.functional.linear(x, weight, bias)
 
 
-def project_add_(x, a, lin):
+def project_add_(x, a, lin, feature="native_to_out"):
     """x += lin(a) in place (the block's residual update, attention.py:527, 567, 572). With enough rows the bias and
     the residual ride in the GEMM's epilogue; returns True then, False when the caller still has to add."""
     if _rows(a) >= NATIVE_LINEAR_MIN_ROWS and linear_plain(lin) and _gemm_shape_ok(lin.weight) and x.is_contiguous() \
-            and _native.FEATURES["native_linears"]:
+            and _native.FEATURES[feature]:
         _native.linear(a, lin.weight, lin.bias, residual=x, out=x)
         return True
     return False
@@ -161,7 +165,7 @@ def transformer_block_forward(self, x, context=None, transformer_options={}):
     n = _attend_add_norm(x, a, self.attn2.to_out, self.norm3)                                       # x += attn2(...)
     ff_in, ff_out = self.ff.net[0], self.ff.net[2]
     h = ff_in(n)
-    if hasattr(ff_in, "proj") and project_add_(x, h, ff_out):
+    if hasattr(ff_in, "proj") and project_add_(x, h, ff_out, "native_ff_out"):
         return x                                     # x += ff.net.2(geglu(n)): bias and residual in the GEMM epilogue
     h = ff_out(self.ff.net[1](h))
     h += x

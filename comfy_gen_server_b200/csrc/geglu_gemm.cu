@@ -64,13 +64,15 @@ constexpr int THREADS = (2 + EPI_WARPS) * 32;
 constexpr int GROUP_M = 8;
 enum { EPI_LINEAR = 0, EPI_GEGLU = 1 };
 
-template <bool PAIR>
+template <bool PAIR, int EPI>
 struct Cfg {
-    static constexpr int STAGES = PAIR ? 6 : 4;
+    // EPI_LINEAR stages the residual tile in shared memory too (32 KiB): one pipeline stage fewer
+    static constexpr int RES_STAGE_BYTES = (EPI == EPI_LINEAR) ? OUT_STAGE_BYTES : 0;
+    static constexpr int STAGES = PAIR ? (EPI == EPI_LINEAR ? 5 : 6) : (EPI == EPI_LINEAR ? 3 : 4);
     static constexpr int B_BYTES = (PAIR ? BN_HALF : UMMA_N) * BK * 2;       // per CTA: 16 / 32 KiB
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TILE_M = PAIR ? 2 * BM : BM;                         // rows per tile (per pair / per CTA)
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGE_BYTES + 256 + 1024;  // + barriers + slack
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGE_BYTES + RES_STAGE_BYTES + 256 + 1024;  // + barriers + slack
 };
 }  // namespace gemm
 
@@ -167,10 +169,11 @@ struct alignas(16) BF8 {
 template <int EPI, bool PAIR>
 __global__ void __launch_bounds__(gemm::THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __grid_constant__ CUtensorMap tmO, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
+            const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR,
+            const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
             __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr) {
     using namespace gemm;
-    using C = Cfg<PAIR>;
+    using C = Cfg<PAIR, EPI>;
     constexpr int STAGES = C::STAGES;
     constexpr int STAGE_BYTES = C::STAGE_BYTES;
     // timing experiments with wrong results are compile-time only (-DCGS_GEMM_EXPT=<bits>, tools/gemm_dbg.sh builds a
@@ -180,11 +183,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     uint8_t* out_stage = smem + STAGES * STAGE_BYTES;
-    uint64_t* full = reinterpret_cast<uint64_t*>(out_stage + OUT_STAGE_BYTES);
+    uint8_t* res_stage = out_stage + OUT_STAGE_BYTES;                 // (EPI_LINEAR) residual tile, same swizzled layout
+    uint64_t* full = reinterpret_cast<uint64_t*>(res_stage + C::RES_STAGE_BYTES);
     uint64_t* empty = full + STAGES;
     uint64_t* tfull = empty + STAGES;
     uint64_t* tempty = tfull + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    uint64_t* rfull = tempty + 2;                                     // residual tile has landed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -201,6 +206,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmO);
+        if (EPI == EPI_LINEAR && residual != nullptr) tma_prefetch_desc(&tmR);
     }
     if (warp == 1) {
         if (elect_one()) {
@@ -212,6 +218,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 mbar_init(&tfull[i], 1);
                 mbar_init(&tempty[i], PAIR ? 2 * EPI_WARPS : EPI_WARPS);   // pair: both CTAs' epilogue warps
             }
+            mbar_init(rfull, 1);
             fence_mbar_init();
         }
         __syncwarp();
@@ -327,6 +334,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 else mbar_arrive(&tempty[acc]);
             }
         };
+        // The residual tile comes in through TMA into a staging tile of the output's swizzled layout: read straight
+        // from global memory it was 64 bytes per thread at a 2.5 KB row stride, which made the epilogue of the K = 1280
+        // projections slower than their mainloop (to_out + residual ran at half the speed of the same GEMM without).
+        const bool use_res = (EPI == EPI_LINEAR) && residual != nullptr;
+        const uint8_t* my_res = res_stage + (cg >> 1) * OUT_BOX_BYTES + row_in_tile * 128;
+        uint32_t res_phase = 0;
+        auto load_residual = [&](int c0, int left, int row_base) {          // store_leader only
+            mbar_expect_tx(rfull, (left > 64 ? 2 : 1) * OUT_BOX_BYTES);
+            tma_load_2d(res_stage, &tmR, rfull, c0, row_base);
+            if (left > 64) tma_load_2d(res_stage + OUT_BOX_BYTES, &tmR, rfull, c0 + 64, row_base);
+        };
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int i = 0; i < n_items; ++i) {
@@ -337,6 +355,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const int row_base = mb * C::TILE_M + (int)rank * BM;
             const int row = row_base + row_in_tile;
             const int col_base = nb * UMMA_N + pc.n_off;        // (EPI_LINEAR) first output column of this piece
+            // (the previous item's last residual reads are behind its second named barrier: the tile is free)
+            if (use_res && store_leader) load_residual(col_base, pc.width, row_base);
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * UMMA_N + (static_cast<uint32_t>(quad * 32) << 16);
@@ -384,13 +404,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if (pass == PASSES - 1) release_acc(acc);
                     // widths are multiples of 32: a 32-column group is all in or all out of the piece
                     const bool col_ok = pass * 128 + cg * 32 < pc.width;
+                    if (use_res) {
+                        mbar_wait(rfull, res_phase);
+                        res_phase ^= 1;
+                    }
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         BF8 bv, rv;
                         const bool use_b = bias != nullptr && col_ok;
-                        const bool use_r = residual != nullptr && col_ok && row < M;
+                        const bool use_r = use_res && col_ok && row < M;
                         if (use_b) bv = *reinterpret_cast<const BF8*>(bias + col + q * 8);
-                        if (use_r) rv = *reinterpret_cast<const BF8*>(residual + (size_t)row * ldr + col + q * 8);
+                        if (use_r) rv = *reinterpret_cast<const BF8*>(my_res + (((chunk0 + q) ^ sw) << 4));
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             float2 fv = make_float2(__uint_as_float(v[q * 8 + 2 * j]),
@@ -410,6 +434,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 // staging tile must no longer be read by the previous TMA store
                 if (store_leader) tma_store_wait_read();
                 named_bar_sync(1, EPI_THREADS);
+                // every thread has its residual values in registers: the second pass's tile may come in
+                if (use_res && store_leader && pass + 1 < PASSES)
+                    load_residual(col_base + (pass + 1) * 128, pc.width - (pass + 1) * 128, row_base);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                     *reinterpret_cast<BF8*>(my_stage + (((chunk0 + q) ^ sw) << 4)) = o[q];
@@ -438,11 +465,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 template <int EPI, bool PAIR>
-static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
+static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
                           const __nv_bfloat16* bp, const __nv_bfloat16* rp, __nv_bfloat16* op, int M, int N, int K,
                           int ldo, int ldr, long long tiles, cudaStream_t stream) {
     using namespace gemm;
-    using C = Cfg<PAIR>;
+    using C = Cfg<PAIR, EPI>;
     auto kern = gemm_kernel<EPI, PAIR>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     const int sms = sm_count();
@@ -465,7 +492,7 @@ static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     cfg.blockDim = dim3(THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = stream;
-    CGS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, bp, rp, op, M, N, K, ldo, ldr));
+    CGS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, tmR, bp, rp, op, M, N, K, ldo, ldr));
     return kOk;
 }
 
@@ -528,6 +555,14 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
         int rc = make_tmap_bf16(&tmO, out, 2, dims, strides, box);
         if (rc != kOk) return rc;
     }
+    CUtensorMap tmR = tmO;
+    if (residual != nullptr) {
+        const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+        const uint64_t strides[1] = {(uint64_t)ldr * 2};
+        const uint32_t box[2] = {64, BM};
+        int rc = make_tmap_bf16(&tmR, residual, 2, dims, strides, box);
+        if (rc != kOk) return rc;
+    }
     const int tiles_n = (epi == EPI_GEGLU) ? N / BN_HALF : (N + UMMA_N - 1) / UMMA_N;
     const long long tiles1 = ((M + BM - 1) / BM) * tiles_n;
     const long long tiles2 = ((M + 2 * BM - 1) / (2 * BM)) * tiles_n;
@@ -542,11 +577,11 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
     auto rp = static_cast<const __nv_bfloat16*>(residual);
     auto op = static_cast<__nv_bfloat16*>(out);
     if (epi == EPI_GEGLU) {
-        return pair ? launch_variant<EPI_GEGLU, true>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
-                    : launch_variant<EPI_GEGLU, false>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
+        return pair ? launch_variant<EPI_GEGLU, true>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
+                    : launch_variant<EPI_GEGLU, false>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
     }
-    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
-                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmO, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
+    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
+                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
 }
 
 }  // namespace cgs
