@@ -281,8 +281,10 @@ def run_ours(args):
     sig = comfy.samplers.calculate_sigmas(model.model_sampling, "karras", SCHEDULE_STEPS).cpu()
     model_k = comfy.samplers.KSamplerX0Inpaint(guider, sig.to(dev))
     x = (noise[my] * float(torch.sqrt(1.0 + sig[0] ** 2.0))).to(dev).contiguous()
-    # per-kernel event brackets only where the step is launched kernel by kernel anyway (GPU-bound batch)
-    time_in_region = per >= 4
+    # The timed region runs the step the way sample() runs it: replayed as one CUDA graph once the probe finds the
+    # host's enqueue time within reach of the GPU's (it does at every batch size here: ~1070 launches per step). A
+    # replay has no per-kernel events, so the per-kernel rooflines come from separate launch-by-launch passes below.
+    time_in_region = False
     if time_in_region:
         _native.time_family("geglu_gemm")       # (also keeps the step out of a CUDA graph: a replay has no per-kernel events)
     fused = FusedDenoise.create(model_k, x, {"model_options": patcher.model_options, "seed": SEED}, sig)

@@ -127,19 +127,23 @@ layernorm_kernel(const __nv_bfloat16* x, const __nv_bfloat16* res,
 //     mean * rstd * gamma) -- 4.5 instructions per element,
 //   * keeps gamma / beta as fp32 in shared memory (conflict-free float4 arrays), filled once per CTA,
 //   * is persistent (3 CTAs per SM) with the NEXT row's 16-byte loads issued before the current row's reductions.
-template <int MAXV>
+// MAXV 16-byte vectors per lane; LASTV lanes hold a valid last vector (32 = the row fills every lane: C = 256 * MAXV).
+// Both are compile-time so that the row loop carries no per-vector bounds tests: with run-time bounds every unrolled
+// vector became its own divergence region (BSSY / BSYNC, BRA.DIV around the shuffles) and a row cost 570 warp
+// instructions, half of them bookkeeping (ncu: issue slots 50 % busy, DRAM 24 %).
+template <int MAXV, int LASTV>
 __global__ void __launch_bounds__(256, 3)
 layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
-                        const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y, long long rows, int C,
-                        float eps) {
-    extern __shared__ float4 gb_smem[];                 // [4][nvec]: gamma lo / hi halves, beta lo / hi halves
+                        const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y, int rows, float eps) {
+    constexpr int NVEC = (MAXV - 1) * 32 + LASTV;
+    constexpr int C = NVEC * 8;
+    extern __shared__ float4 gb_smem[];                 // [4][NVEC]: gamma lo / hi halves, beta lo / hi halves
     const int lane = threadIdx.x & 31;
-    const int nvec = C >> 3;
     float4* g_lo = gb_smem;
-    float4* g_hi = g_lo + nvec;
-    float4* b_lo = g_hi + nvec;
-    float4* b_hi = b_lo + nvec;
-    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+    float4* g_hi = g_lo + NVEC;
+    float4* b_lo = g_hi + NVEC;
+    float4* b_hi = b_lo + NVEC;
+    for (int v = threadIdx.x; v < NVEC; v += blockDim.x) {
         const Vec8 g = reinterpret_cast<const Vec8*>(gamma)[v];
         const Vec8 b = reinterpret_cast<const Vec8*>(beta)[v];
         const float2 g0 = __bfloat1622float2(g.v[0]), g1 = __bfloat1622float2(g.v[1]);
@@ -152,15 +156,20 @@ layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16
         b_hi[v] = make_float4(b2.x, b2.y, b3.x, b3.y);
     }
     __syncthreads();
-    const long long stride = (long long)gridDim.x * (blockDim.x >> 5);
-    long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= rows) return;
+    const int stride = gridDim.x * (blockDim.x >> 5);
+    int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const bool last_ok = LASTV == 32 || lane < LASTV;      // this lane holds a vector in the last position
+    const Vec8* xv = reinterpret_cast<const Vec8*>(x) + lane;
+    Vec8* yv = reinterpret_cast<Vec8*>(y) + lane;
     Vec8 nxt[MAXV];
+    const Vec8 zero = {};
+    if (row < rows) {
+        const Vec8* p = xv + (size_t)row * NVEC;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i)
-        if (lane + i * 32 < nvec) nxt[i] = ld_stream(reinterpret_cast<const Vec8*>(x + row * C) + lane + i * 32);
-    const float inv_c = 1.0f / (float)C;
-    while (row < rows) {
+        for (int i = 0; i < MAXV; ++i) nxt[i] = (i < MAXV - 1 || last_ok) ? ld_stream(p + i * 32) : zero;
+    }
+    constexpr float inv_c = 1.0f / (float)C;
+    for (; row < rows; row += stride) {
         // bf16 pair -> packed fp32 pair: the low half shifted up, the high half masked
         uint64_t a[MAXV][4];
 #pragma unroll
@@ -169,19 +178,16 @@ layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16
 #pragma unroll
             for (int j = 0; j < 4; ++j) a[i][j] = pack_u32x2(w[j] << 16, w[j] & 0xffff0000u);
         }
-        const long long next = row + stride;
-        if (next < rows) {
+        if (row + stride < rows) {
+            const Vec8* p = xv + (size_t)(row + stride) * NVEC;
 #pragma unroll
-            for (int i = 0; i < MAXV; ++i)
-                if (lane + i * 32 < nvec) nxt[i] = ld_stream(reinterpret_cast<const Vec8*>(x + next * C) + lane + i * 32);
+            for (int i = 0; i < MAXV; ++i) nxt[i] = (i < MAXV - 1 || last_ok) ? ld_stream(p + i * 32) : zero;
         }
         uint64_t s2 = 0ull;
 #pragma unroll
         for (int i = 0; i < MAXV; ++i) {
-            if (lane + i * 32 < nvec) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) s2 = fadd2(s2, a[i][j]);
-            }
+            for (int j = 0; j < 4; ++j) s2 = fadd2(s2, a[i][j]);        // (absent vectors are zeros)
         }
         float s_lo, s_hi;
         unpack_f32x2(s2, s_lo, s_hi);
@@ -190,29 +196,30 @@ layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16
         uint64_t q2 = 0ull;
 #pragma unroll
         for (int i = 0; i < MAXV; ++i) {
-            if (lane + i * 32 < nvec) {
+            uint64_t qi = 0ull;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint64_t d2 = fadd2(a[i][j], negmean2);
-                    q2 = ffma2(d2, d2, q2);
-                }
+            for (int j = 0; j < 4; ++j) {
+                const uint64_t d2 = fadd2(a[i][j], negmean2);
+                qi = ffma2(d2, d2, qi);
             }
+            if (i < MAXV - 1 || last_ok) q2 = fadd2(q2, qi);           // (a select, not a branch)
         }
         float q_lo, q_hi;
         unpack_f32x2(q2, q_lo, q_hi);
         const float rstd = rsqrtf(warp_sum(q_lo + q_hi) * inv_c + eps);
         const uint64_t rstd2 = pack_f32x2(rstd, rstd);
-        Vec8* yr = reinterpret_cast<Vec8*>(y + row * C);
+        Vec8* yr = yv + (size_t)row * NVEC;
 #pragma unroll
         for (int i = 0; i < MAXV; ++i) {
             const int v = lane + i * 32;
-            if (v < nvec) {
+            if (i < MAXV - 1 || last_ok) {
                 const float4 gl = g_lo[v], gh = g_hi[v], bl = b_lo[v], bh = b_hi[v];
                 const uint64_t g2[4] = {pack_f32x2(gl.x, gl.y), pack_f32x2(gl.z, gl.w), pack_f32x2(gh.x, gh.y),
                                         pack_f32x2(gh.z, gh.w)};
                 const uint64_t b2[4] = {pack_f32x2(bl.x, bl.y), pack_f32x2(bl.z, bl.w), pack_f32x2(bh.x, bh.y),
                                         pack_f32x2(bh.z, bh.w)};
-                uint32_t o[4];
+                Vec8 ov;
+                uint32_t* ow = reinterpret_cast<uint32_t*>(&ov);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const uint64_t gs = ffma2(g2[j], rstd2, 0ull);             // rstd * gamma
@@ -220,15 +227,11 @@ layernorm_stream_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16
                     const uint64_t y2 = ffma2(a[i][j], gs, bs);
                     float lo, hi;
                     unpack_f32x2(y2, lo, hi);
-                    o[j] = pack_bf16x2(lo, hi);
+                    ow[j] = pack_bf16x2(lo, hi);
                 }
-                Vec8 ov;
-                uint32_t* ow = reinterpret_cast<uint32_t*>(&ov);
-                ow[0] = o[0]; ow[1] = o[1]; ow[2] = o[2]; ow[3] = o[3];
-                yr[v] = ov;
+                yr[i * 32] = ov;
             }
         }
-        row = next;
     }
 }
 
@@ -252,19 +255,27 @@ static int launch_ln(const void* x, const void* res, const void* gamma, const vo
     auto bp = static_cast<const __nv_bfloat16*>(beta);
     auto xo = static_cast<__nv_bfloat16*>(x_out);
     auto yp = static_cast<__nv_bfloat16*>(y);
-    if (!ADD && C <= 1280) {
-        // packed-math persistent variant (see layernorm_stream_kernel)
+    if (!ADD && rows < 0x7fffffffLL / 160) {
+        // packed-math persistent variant (see layernorm_stream_kernel) for the UNets' channel counts
         const long long resident = (long long)sm_count() * 3;
         const unsigned pgrid = (unsigned)(grid < resident ? grid : resident);
         const size_t smem = (size_t)(C >> 3) * 4 * sizeof(float4);
-        if (C <= 512)
-            layernorm_stream_kernel<2><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, rows, C, eps);
-        else if (C <= 768)
-            layernorm_stream_kernel<3><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, rows, C, eps);
-        else
-            layernorm_stream_kernel<5><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, rows, C, eps);
-        CGS_CUDA_CHECK(cudaGetLastError());
-        return kOk;
+        const int r = (int)rows;
+        bool done = true;
+        switch (C) {
+            case 1280: layernorm_stream_kernel<5, 32><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            case 1024: layernorm_stream_kernel<4, 32><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            case 768: layernorm_stream_kernel<3, 32><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            case 640: layernorm_stream_kernel<3, 16><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            case 512: layernorm_stream_kernel<2, 32><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            case 320: layernorm_stream_kernel<2, 8><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            case 256: layernorm_stream_kernel<1, 32><<<pgrid, warps * 32, smem, stream>>>(xp, gp, bp, yp, r, eps); break;
+            default: done = false;
+        }
+        if (done) {
+            CGS_CUDA_CHECK(cudaGetLastError());
+            return kOk;
+        }
     }
     if (C <= 512)
         layernorm_kernel<2, ADD><<<grid, warps * 32, 0, stream>>>(xp, rp, gp, bp, xo, yp, rows, C, eps);

@@ -39,10 +39,7 @@ def timeit(fn, iters=10, warmup=3, flush=True):
     times = []
     for _ in range(iters):
         if flush:
-            # evict the L2 with CLEAN lines (a read pass over 256 MiB): zeroing the buffer instead leaves 126 MB of
-            # dirty lines whose write-back is then charged to the kernel under test (it halved the bandwidth of the
-            # 84 MB LayerNorm launches in round 1's numbers)
-            _flush.sum()
+            _flush.zero_()          # flush L2: write a buffer larger than L2 (profiling recipe)
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         fn()
