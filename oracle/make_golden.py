@@ -336,8 +336,29 @@ def gen_sd21v_full(seed=47, hw=96, steps=25, first_steps=3, name="e2e_sd21v_full
          ref_threads=np.int64(torch.get_num_threads()))
 
 
+VAE_DDCONFIG = {'double_z': True, 'z_channels': 4, 'resolution': 256, 'in_channels': 3, 'out_ch': 3, 'ch': 128,
+                'ch_mult': [1, 2, 4, 4], 'num_res_blocks': 2, 'attn_resolutions': [], 'dropout': 0.0}
+
+
+def gen_vae_decode(seed=48, hw=32):
+    """The step after the path: the SD / SDXL VAE decoder (comfy/ldm/modules/diffusionmodules/
+    model.py:542-660, the configuration of comfy/sd.py:213) on a seeded latent, fp32 on the CPU."""
+    import comfy.ldm.modules.diffusionmodules.model as vm
+    dec = vm.Decoder(**VAE_DDCONFIG)
+    shapes = {k: tuple(v.shape) for k, v in dec.state_dict().items()}
+    dec.load_state_dict(uc.seeded_state_dict(shapes, seed, residual_damp=1.0))
+    z = randn((2, 4, hw, hw), seed + 1)
+    with torch.inference_mode():
+        img = dec(z)
+    print(f"vae_decode: out {tuple(img.shape)} std {img.std():.4f}")
+    save("vae_decode", z=z, image=img, seed=np.int64(seed))
+
+
 def main():
     torch.manual_seed(0)
+    if "--only-vae" in sys.argv:
+        gen_vae_decode()
+        return
     if "--only-sd21v-full" in sys.argv:
         gen_sd21v_full()
         return
