@@ -266,7 +266,7 @@ def run_ours(args):
 
     integration.install()
     if args.native is not None:         # A/B: which of the block's projections run on the library GEMM
-        for f in ("qkv", "to_out", "ff_out"):
+        for f in ("qkv", "to_out", "ff_out", "conv", "skip"):
             _native.FEATURES["native_" + f] = f in args.native.split(",")
 
     # ---- device-resident leg: K denoise steps through the fused step of the drop-in --------------
@@ -483,7 +483,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-library-baseline", action="store_true")
-    ap.add_argument("--native", default=None, help="A/B: comma list of qkv,to_out,ff_out on the library GEMM")
+    ap.add_argument("--native", default=None, help="A/B: comma list of qkv,to_out,ff_out,conv,skip on the library GEMM")
     ap.add_argument("--profile", action="store_true",
                     help="only the timed denoise steps, bracketed by cudaProfilerStart/Stop (for ncu)")
     args = ap.parse_args()

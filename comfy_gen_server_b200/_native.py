@@ -37,6 +37,7 @@ _SIGNATURES = {
     "cgs_geglu_gemm_fwd": [_c_void_p] * 4 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_gemm_set_variant": [_c_int],
+    "cgs_conv3x3_nhwc_fwd": [_c_void_p] * 5 + [_c_int] * 5 + [_c_ll] * 3 + [_c_void_p],
     "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
     "cgs_cfg_denoise_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                               _c_ll, _c_ll, _c_void_p],
@@ -320,7 +321,10 @@ FEATURES = {"residual_add": True, "cat_channels": True, "upsample2x": True, "fol
             # which Linear layers of the transformer block run on this library's GEMM (block.py): measured in-step on
             # SDXL 1024^2 batch 8 (profiles/r02_linear_routing.json): to_out + ff.net.2 with the residual add in the
             # epilogue 111.5 ms / step, nothing 112.5, all three 112.0, ff.net.2 alone 113.4
-            "native_qkv": False, "native_to_out": True, "native_ff_out": True}
+            "native_qkv": False, "native_to_out": True, "native_ff_out": True,
+            # 3x3 convolutions of the ResBlocks / Upsample on this library's implicit GEMM instead of cuDNN
+            # (native_skip: the ResBlock's 1x1 skip convolution as a plain GEMM over the pixel rows)
+            "native_conv": True, "native_skip": False}
 
 
 def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
@@ -476,6 +480,51 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
                                            out.data_ptr(), M, N, K, x2.stride(0), weight.stride(0), N, N,
                                            _stream(x))
     _check(rc, "cgs_linear_fwd")
+    return out
+
+
+def conv3x3_tile_efficiency(h: int, w: int) -> float:
+    """Share of a pixel tile's 128 rows that are real pixels for an h x w image (the kernel tiles an image into
+    TH x TW rectangles, TW the largest power of two dividing w, TH = 128 / TW)."""
+    tw = 1
+    while tw < 128 and w % (tw * 2) == 0:
+        tw *= 2
+    th = 128 // tw
+    return h / (-(-h // th) * th)
+
+
+def conv3x3(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
+            residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """F.conv2d(x, weight, bias, stride 1, padding 1) (+ residual) for channels-last bf16 images and a channels-last
+    [Cout, Cin, 3, 3] weight, as an implicit GEMM on the tensor cores. x may be a channel slice of a wider
+    channels-last buffer."""
+    _require_cuda("conv3x3 x", x, torch.bfloat16)
+    _require_cuda("conv3x3 weight", weight, torch.bfloat16)
+    if x.dim() != 4 or weight.dim() != 4 or tuple(weight.shape[2:]) != (3, 3) or weight.shape[1] != x.shape[1]:
+        raise RuntimeError(f"conv3x3: x {tuple(x.shape)} / weight {tuple(weight.shape)}")
+    n, cin, h, w = x.shape
+    cout = weight.shape[0]
+    if not weight.is_contiguous(memory_format=torch.channels_last):
+        raise RuntimeError("conv3x3: weight must be channels-last ([Cout, 3, 3, Cin] in memory)")
+    sn, sc, sh, sw = x.stride()
+    if n and not (sc == 1 and sh == w * sw and (n == 1 or sn == h * w * sw)):
+        raise RuntimeError(f"conv3x3: x must be channels-last with dense pixels (strides {x.stride()})")
+    out = torch.empty((n, cout, h, w), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    r_ptr = None
+    if residual is not None:
+        _require_cuda("conv3x3 residual", residual, torch.bfloat16)
+        if residual.shape != out.shape or residual.stride() != out.stride():
+            raise RuntimeError("conv3x3: residual must be a dense channels-last tensor of the output's shape")
+        r_ptr = residual.data_ptr()
+    if bias is not None:
+        _require_cuda("conv3x3 bias", bias, torch.bfloat16)
+        if bias.numel() != cout or not bias.is_contiguous():
+            raise RuntimeError("conv3x3: bias must be contiguous [Cout]")
+    with _Launch("conv3x3", x, 2.0 * n * h * w * 9 * cin * cout):
+        rc = load_library().cgs_conv3x3_nhwc_fwd(x.data_ptr(), weight.data_ptr(),
+                                                 bias.data_ptr() if bias is not None else None, r_ptr, out.data_ptr(),
+                                                 n, h, w, cin, cout, sw if n else cin, cout, cout, _stream(x))
+    _check(rc, "cgs_conv3x3_nhwc_fwd")
     return out
 
 

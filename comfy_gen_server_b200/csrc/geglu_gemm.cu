@@ -42,7 +42,24 @@
 // global memory -- was built and measured first: 19 MB of fp32 partials per launch cost as much as the idle SMs.)
 // The same mechanism serves the last column of tiles when N is not a multiple of 256 (N = 640: an N = 128 MMA).
 //
-// Tensor-core bound. Algorithmic FLOPs = 2 * M * K * (2N) for GEGLU, 2 * M * K * N for linear.
+//
+// CONV (EPI_LINEAR, CTA pairs): the same GEMM as a 3x3 / stride 1 / pad 1 convolution over a channels-last image
+// (reference: ResBlock / Upsample convolutions, comfy/ldm/modules/diffusionmodules/openaimodel.py:83-96, 177-232;
+// operator comfy/ops.py:67-80), implicit -- no im2col matrix exists anywhere. A tile's 128 rows are a TH x TW
+// rectangle of pixels of one image; k-block (tap r,s ; 64 channels) of its A operand is ONE 4-D TMA box
+// {64 ch, TW, TH, 1} starting at pixel (h0 + r - 1, w0 + s - 1): the tensor map's out-of-bounds zero fill IS the
+// padding, and the box lands in shared memory in exactly the K-major, 128-byte-swizzled [128 x 64] layout the MMA
+// reads. B is the weight as stored in channels-last memory, [Cout][3][3][Cin] = [Cout, 9 Cin] K-major. Output and
+// residual tiles use 4-D maps of the same box, so bias + residual (ResBlock: `skip(x) + h`) ride in the epilogue.
+//
+// WIDE (N a multiple of 320: the 320-channel level of every SD / SDXL UNet): 256 + 64 columns as two tiles would load
+// A twice and run the 64-column tile at a quarter of the arithmetic intensity (bound by the operand feed: 77 %).
+// Instead one tile is 320 columns: two MMAs per k-step (N = 256 and N = 64) on the same A tile, accumulator
+// 320 TMEM columns, single-buffered (640 would not fit): the epilogue's TMEM reads are exposed (~5 % of a K = 2880
+// mainloop), the A traffic halves.
+//
+// Tensor-core bound. Algorithmic FLOPs = 2 * M * K * (2N) for GEGLU, 2 * M * K * N for linear, 2 * pixels * 9 Cin * Cout
+// for the convolution.
 #include "common.cuh"
 
 #ifndef CGS_GEMM_EXPT
@@ -64,12 +81,28 @@ constexpr int THREADS = (2 + EPI_WARPS) * 32;
 constexpr int GROUP_M = 8;
 enum { EPI_LINEAR = 0, EPI_GEGLU = 1 };
 
-template <bool PAIR, int EPI>
+constexpr int WIDE_N = 320;                   // WIDE tiles: 256 + 64 columns
+constexpr int B2_ROWS = (WIDE_N - UMMA_N) / 2; // rows of the second B box per CTA
+constexpr int B2_BYTES = B2_ROWS * BK * 2;    // 4 KiB
+
+// a tile's rows as a rectangle of pixels (CONV)
+struct ConvGeom {
+    int H, W, TH, TW, tiles_h, tiles_w, n_img, cin, cblocks;
+    int whole_tiles;      // != 0: the last round is not dealt out in column pieces (measurement switch)
+};
+
+template <bool PAIR, int EPI, bool WIDE = false>
 struct Cfg {
+    static_assert(!WIDE || (PAIR && EPI == EPI_LINEAR), "WIDE tiles exist for linear epilogues on CTA pairs");
     // EPI_LINEAR stages the residual tile in shared memory too (32 KiB): one pipeline stage fewer
-    static constexpr int RES_STAGE_BYTES = (EPI == EPI_LINEAR) ? OUT_STAGE_BYTES : 0;
-    static constexpr int STAGES = PAIR ? (EPI == EPI_LINEAR ? 5 : 6) : (EPI == EPI_LINEAR ? 3 : 4);
-    static constexpr int B_BYTES = (PAIR ? BN_HALF : UMMA_N) * BK * 2;       // per CTA: 16 / 32 KiB
+    // (experiment bit 16: no residual staging, one more stage -- residual must be NULL)
+    static constexpr bool RES = (EPI == EPI_LINEAR) && !(CGS_GEMM_EXPT & 16);
+    static constexpr int RES_STAGE_BYTES = RES ? OUT_STAGE_BYTES : 0;
+    static constexpr int STAGES = (WIDE ? 4 : PAIR ? (EPI == EPI_LINEAR ? 5 : 6) : (EPI == EPI_LINEAR ? 3 : 4)) +
+                                  ((EPI == EPI_LINEAR && !RES) ? 1 : 0);
+    static constexpr int B_BYTES = (PAIR ? BN_HALF : UMMA_N) * BK * 2 + (WIDE ? B2_BYTES : 0);   // per CTA: 16 / 20 / 32 KiB
+    static constexpr int TILE_N = WIDE ? WIDE_N : UMMA_N;                     // output columns per tile (EPI_LINEAR)
+    static constexpr int GROUPS = TILE_N / 64;                                // 64-column groups per tile
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TILE_M = PAIR ? 2 * BM : BM;                         // rows per tile (per pair / per CTA)
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_STAGE_BYTES + RES_STAGE_BYTES + 256 + 1024;  // + barriers + slack
@@ -111,30 +144,33 @@ struct Piece {
 };
 
 // Full rounds: worker w takes tiles w, w + W, ... whole. Last, partly filled round (rem < W tiles), EPI_LINEAR only:
-// its rem * 4 column groups (64 columns each) are dealt out contiguously and evenly to all workers, so a worker gets
+// its rem * G column groups (64 columns each; G = 4, or 5 for WIDE tiles) are dealt out contiguously and evenly to all workers, so a worker gets
 // the end of one tile and / or the beginning of the next.
-template <int EPI>
+template <int EPI, int TILE_N = gemm::UMMA_N>
 struct Schedule {
+    static constexpr int G = TILE_N / 64;
     int workers, num_tiles, tiles_m, tiles_n, N, full_rounds, rem, active, groups;
-    __device__ Schedule(int workers_, int tiles_m_, int tiles_n_, int N_)
-        : workers(workers_), num_tiles(tiles_m_ * tiles_n_), tiles_m(tiles_m_), tiles_n(tiles_n_), N(N_) {
+    bool split;
+    __device__ Schedule(int workers_, int tiles_m_, int tiles_n_, int N_, bool split_ = true)
+        : workers(workers_), num_tiles(tiles_m_ * tiles_n_), tiles_m(tiles_m_), tiles_n(tiles_n_), N(N_),
+          split(split_ && EPI == gemm::EPI_LINEAR) {
         full_rounds = num_tiles / workers;
         rem = num_tiles - full_rounds * workers;
-        groups = rem * 4;
-        active = (EPI == gemm::EPI_LINEAR) ? (groups < workers ? groups : workers) : rem;
+        groups = rem * G;
+        active = split ? (groups < workers ? groups : workers) : rem;
     }
     __device__ int tile_width(int tile) const {
         if (EPI == gemm::EPI_GEGLU) return gemm::UMMA_N;
         int mb, nb;
         tile_coords(tile, tiles_m, tiles_n, mb, nb);
-        const int left = N - nb * gemm::UMMA_N;
-        return left < gemm::UMMA_N ? left : gemm::UMMA_N;
+        const int left = N - nb * TILE_N;
+        return left < TILE_N ? left : TILE_N;
     }
     __device__ int items(int w) const {
         if (w >= active) return full_rounds;
-        if (EPI == gemm::EPI_GEGLU) return full_rounds + 1;
+        if (!split) return full_rounds + 1;
         const int a = (int)((long long)groups * w / active), b = (int)((long long)groups * (w + 1) / active);
-        return full_rounds + ((b - 1) / 4 - a / 4) + 1;
+        return full_rounds + ((b - 1) / G - a / G) + 1;
     }
     __device__ Piece item(int w, int i) const {
         Piece p;
@@ -144,15 +180,15 @@ struct Schedule {
             p.width = tile_width(p.tile);
             return p;
         }
-        if (EPI == gemm::EPI_GEGLU) {
+        if (!split) {
             p.tile = full_rounds * workers + w;
-            p.width = gemm::UMMA_N;
+            p.width = tile_width(p.tile);
             return p;
         }
         const int a = (int)((long long)groups * w / active), b = (int)((long long)groups * (w + 1) / active);
-        const int slot = a / 4 + (i - full_rounds);
-        const int g0 = (a > slot * 4 ? a : slot * 4) - slot * 4;
-        const int g1 = (b < slot * 4 + 4 ? b : slot * 4 + 4) - slot * 4;
+        const int slot = a / G + (i - full_rounds);
+        const int g0 = (a > slot * G ? a : slot * G) - slot * G;
+        const int g1 = (b < slot * G + G ? b : slot * G + G) - slot * G;
         p.tile = full_rounds * workers + slot;
         p.n_off = g0 * 64;
         const int have = tile_width(p.tile) - p.n_off;
@@ -166,14 +202,28 @@ struct alignas(16) BF8 {
     __nv_bfloat162 v[4];
 };
 
-template <int EPI, bool PAIR>
+// 128-row tile index -> image, first pixel row / column of its TH x TW rectangle (n >= n_img: a tile past the end,
+// its loads come back as zeros and its stores are clipped)
+__device__ __forceinline__ void conv_tile(const gemm::ConvGeom& g, int mt, int& n, int& h0, int& w0) {
+    const int per_img = g.tiles_h * g.tiles_w;
+    n = mt / per_img;
+    const int r = mt - n * per_img;
+    const int ht = r / g.tiles_w;
+    h0 = ht * g.TH;
+    w0 = (r - ht * g.tiles_w) * g.TW;
+}
+
+template <int EPI, bool PAIR, bool CONV = false, bool WIDE = false>
 __global__ void __launch_bounds__(gemm::THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmB2,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR,
             const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* residual,
-            __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr) {
+            __nv_bfloat16* out, int M, int N, int K, int ldo, int ldr, const gemm::ConvGeom geom) {
     using namespace gemm;
-    using C = Cfg<PAIR, EPI>;
+    static_assert(!CONV || (PAIR && EPI == EPI_LINEAR), "the convolution runs on CTA pairs with the linear epilogue");
+    using C = Cfg<PAIR, EPI, WIDE>;
+    constexpr int TILE_N = C::TILE_N;
     constexpr int STAGES = C::STAGES;
     constexpr int STAGE_BYTES = C::STAGE_BYTES;
     // timing experiments with wrong results are compile-time only (-DCGS_GEMM_EXPT=<bits>, tools/gemm_dbg.sh builds a
@@ -197,14 +247,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int worker = PAIR ? (blockIdx.x >> 1) : blockIdx.x;   // pair (or CTA) index
     const int workers = PAIR ? (gridDim.x >> 1) : gridDim.x;
     const int tiles_m = (M + C::TILE_M - 1) / C::TILE_M;
-    const int tiles_n = (EPI == EPI_GEGLU) ? (N / BN_HALF) : ((N + UMMA_N - 1) / UMMA_N);
-    const int kblocks = (K + BK - 1) / BK;
-    const Schedule<EPI> sched(workers, tiles_m, tiles_n, N);
+    const int tiles_n = (EPI == EPI_GEGLU) ? (N / BN_HALF) : ((N + TILE_N - 1) / TILE_N);
+    const int kblocks = CONV ? 9 * geom.cblocks : (K + BK - 1) / BK;
+    const Schedule<EPI, TILE_N> sched(workers, tiles_m, tiles_n, N, geom.whole_tiles == 0);
     const int n_items = sched.items(worker);
 
     if (warp == 0 && elect_one()) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        if (WIDE) tma_prefetch_desc(&tmB2);
         tma_prefetch_desc(&tmO);
         if (EPI == EPI_LINEAR && residual != nullptr) tma_prefetch_desc(&tmR);
     }
@@ -246,21 +297,39 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 int mb, nb;
                 tile_coords(pc.tile, tiles_m, tiles_n, mb, nb);
                 const int m0 = mb * C::TILE_M + (int)rank * BM;
+                int img = 0, h0 = 0, w0 = 0;
+                if (CONV) conv_tile(geom, mb * 2 + (int)rank, img, h0, w0);
                 // B rows of this piece. GEGLU: value rows + gate rows of the tile's 128 output columns. Linear: `width`
                 // consecutive rows of W; with CTA pairs each CTA stages half of them (a full 128-row box is loaded,
                 // the MMA reads the first width / 2 rows of it).
-                const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * UMMA_N + pc.n_off;
-                const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : row0 + (PAIR ? pc.width / 2 : BN_HALF);
+                // WIDE, a whole 320-column tile: 128 + 32 rows per CTA (columns [0, 256) and [256, 320) of the tile)
+                const bool wide_piece = WIDE && pc.width > UMMA_N;
+                const int w1 = wide_piece ? UMMA_N : pc.width;
+                const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * TILE_N + pc.n_off;
+                const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : row0 + (PAIR ? w1 / 2 : BN_HALF);
                 const bool two_boxes = PAIR || pc.width > BN_HALF;
+                int tap = 0, cb = 0;                       // (CONV) filter tap 0..8 and 64-channel block inside it
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
                     if (PAIR) {
                         // both CTAs' bytes are credited to the leader's barrier; the leader announces them
-                        if (rank == 0) mbar_expect_tx(&full[stage], 2 * STAGE_BYTES);
-                        tma_load_2d_pair(sa, &tmA, &full[stage], kb * BK, m0);
-                        tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, rank == 0 ? row0 : row1);
+                        if (rank == 0)
+                            mbar_expect_tx(&full[stage], 2 * (A_BYTES + BN_HALF * BK * 2 + (wide_piece ? B2_BYTES : 0)));
+                        int kcoord = kb * BK;
+                        if (CONV) {
+                            const int r = tap / 3, sft = tap - 3 * r;
+                            tma_load_4d_pair(sa, &tmA, &full[stage], cb * BK, w0 + sft - 1, h0 + r - 1, img);
+                            kcoord = tap * geom.cin + cb * BK;
+                            if (++cb == geom.cblocks) { cb = 0; ++tap; }
+                        } else {
+                            tma_load_2d_pair(sa, &tmA, &full[stage], kcoord, m0);
+                        }
+                        tma_load_2d_pair(sb, &tmB, &full[stage], kcoord, rank == 0 ? row0 : row1);
+                        if (wide_piece)
+                            tma_load_2d_pair(sb + BN_HALF * BK * 2, &tmB2, &full[stage], kcoord,
+                                             row0 + UMMA_N + (int)rank * B2_ROWS);
                     } else {
                         mbar_expect_tx(&full[stage], two_boxes ? STAGE_BYTES : A_BYTES + BN_HALF * BK * 2);
                         tma_load_2d(sa, &tmA, &full[stage], kb * BK, m0);
@@ -287,7 +356,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             for (int i = 0; i < n_items; ++i) {
                 const Piece pc = sched.item(worker, i);
                 if (pc.width <= 0) continue;
-                const uint32_t idesc = umma_idesc_bf16(C::TILE_M, pc.width, 0);
+                const bool wide_piece = WIDE && pc.width > UMMA_N;
+                const uint32_t idesc = umma_idesc_bf16(C::TILE_M, wide_piece ? UMMA_N : pc.width, 0);
+                const uint32_t idesc2 = umma_idesc_bf16(C::TILE_M, WIDE_N - UMMA_N, 0);
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * UMMA_N;
@@ -305,11 +376,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                             else umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
                         }
                     }
+                    if (wide_piece) {          // columns [256, 320) of the tile: same A, the CTA's second B box
+                        const uint64_t b2desc = umma_desc_sw128(sa + A_BYTES + BN_HALF * BK * 2, 16, 1024);
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k)
+                            umma_ss_pair(d_tmem + UMMA_N, adesc + 2 * k, b2desc + 2 * k, idesc2, (kb | k) != 0);
+                    }
                     if (PAIR) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 if (PAIR) tc_commit_pair(&tfull[acc]); else tc_commit(&tfull[acc]);
-                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+                if (WIDE) acc_phase ^= 1;                       // one accumulator buffer
+                else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
         __syncwarp();
@@ -337,13 +415,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         // The residual tile comes in through TMA into a staging tile of the output's swizzled layout: read straight
         // from global memory it was 64 bytes per thread at a 2.5 KB row stride, which made the epilogue of the K = 1280
         // projections slower than their mainloop (to_out + residual ran at half the speed of the same GEMM without).
-        const bool use_res = (EPI == EPI_LINEAR) && residual != nullptr;
+        const bool use_res = C::RES && residual != nullptr;
         const uint8_t* my_res = res_stage + (cg >> 1) * OUT_BOX_BYTES + row_in_tile * 128;
         uint32_t res_phase = 0;
+        int img = 0, h0 = 0, w0 = 0;                                          // (CONV) this CTA's pixel rectangle
         auto load_residual = [&](int c0, int left, int row_base) {          // store_leader only
             mbar_expect_tx(rfull, (left > 64 ? 2 : 1) * OUT_BOX_BYTES);
-            tma_load_2d(res_stage, &tmR, rfull, c0, row_base);
-            if (left > 64) tma_load_2d(res_stage + OUT_BOX_BYTES, &tmR, rfull, c0 + 64, row_base);
+            if (CONV) {
+                tma_load_4d(res_stage, &tmR, rfull, c0, w0, h0, img);
+                if (left > 64) tma_load_4d(res_stage + OUT_BOX_BYTES, &tmR, rfull, c0 + 64, w0, h0, img);
+            } else {
+                tma_load_2d(res_stage, &tmR, rfull, c0, row_base);
+                if (left > 64) tma_load_2d(res_stage + OUT_BOX_BYTES, &tmR, rfull, c0 + 64, row_base);
+            }
         };
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -354,13 +438,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             tile_coords(pc.tile, tiles_m, tiles_n, mb, nb);
             const int row_base = mb * C::TILE_M + (int)rank * BM;
             const int row = row_base + row_in_tile;
-            const int col_base = nb * UMMA_N + pc.n_off;        // (EPI_LINEAR) first output column of this piece
+            const int col_base = nb * TILE_N + pc.n_off;        // (EPI_LINEAR) first output column of this piece
+            if (CONV) conv_tile(geom, mb * 2 + (int)rank, img, h0, w0);
             // (the previous item's last residual reads are behind its second named barrier: the tile is free)
             if (use_res && store_leader) load_residual(col_base, pc.width, row_base);
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * UMMA_N + (static_cast<uint32_t>(quad * 32) << 16);
-            const int PASSES = (EPI == EPI_GEGLU) ? 1 : (pc.width > 128 ? 2 : 1);
+            const int PASSES = (EPI == EPI_GEGLU) ? 1 : (pc.width + 127) / 128;
 #pragma unroll 1
             for (int pass = 0; pass < PASSES; ++pass) {
                 BF8 o[4];
@@ -412,7 +497,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     for (int q = 0; q < 4; ++q) {
                         BF8 bv, rv;
                         const bool use_b = bias != nullptr && col_ok;
-                        const bool use_r = use_res && col_ok && row < M;
+                        const bool use_r = use_res && col_ok && (CONV || row < M);   // (CONV: rows outside come back 0)
                         if (use_b) bv = *reinterpret_cast<const BF8*>(bias + col + q * 8);
                         if (use_r) rv = *reinterpret_cast<const BF8*>(my_res + (((chunk0 + q) ^ sw) << 4));
 #pragma unroll
@@ -442,16 +527,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     *reinterpret_cast<BF8*>(my_stage + (((chunk0 + q) ^ sw) << 4)) = o[q];
                 fence_proxy_async_smem();
                 named_bar_sync(1, EPI_THREADS);
-                if (store_leader && !(dbg & 2) && row_base < M) {
+                if (store_leader && !(dbg & 2) && (CONV ? img < geom.n_img : row_base < M)) {
                     // 64-column boxes; pieces are multiples of 64 columns except at the edge of N, where the tensor map clips
                     const int c0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : col_base + pass * 128;
                     const int left = (EPI == EPI_GEGLU) ? BN_HALF : pc.width - pass * 128;
-                    if (left > 0) tma_store_2d(&tmO, out_stage, c0, row_base);
-                    if (left > 64) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, row_base);
+                    if (CONV) {
+                        if (left > 0) tma_store_4d(&tmO, out_stage, c0, w0, h0, img);
+                        if (left > 64) tma_store_4d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, w0, h0, img);
+                    } else {
+                        if (left > 0) tma_store_2d(&tmO, out_stage, c0, row_base);
+                        if (left > 64) tma_store_2d(&tmO, out_stage + OUT_BOX_BYTES, c0 + 64, row_base);
+                    }
                     tma_store_commit();
                 }
             }
-            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            if (WIDE) acc_phase ^= 1;
+            else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (store_leader) tma_store_wait_all();
     }
@@ -464,19 +555,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
 }
 
-template <int EPI, bool PAIR>
-static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
-                          const __nv_bfloat16* bp, const __nv_bfloat16* rp, __nv_bfloat16* op, int M, int N, int K,
-                          int ldo, int ldr, long long tiles, cudaStream_t stream) {
+template <int EPI, bool PAIR, bool CONV = false, bool WIDE = false>
+static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmB2, const CUtensorMap& tmO,
+                          const CUtensorMap& tmR, const __nv_bfloat16* bp, const __nv_bfloat16* rp, __nv_bfloat16* op,
+                          int M, int N, int K, int ldo, int ldr, const gemm::ConvGeom& geom, long long tiles,
+                          cudaStream_t stream) {
     using namespace gemm;
-    using C = Cfg<PAIR, EPI>;
-    auto kern = gemm_kernel<EPI, PAIR>;
+    using C = Cfg<PAIR, EPI, WIDE>;
+    auto kern = gemm_kernel<EPI, PAIR, CONV, WIDE>;
     CGS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     const int sms = sm_count();
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
     // EPI_LINEAR deals the last round out in 64-column pieces: up to 4 workers per tile can be put to use
-    const long long useful = (EPI == EPI_LINEAR) ? tiles * 4 : tiles;
+    const long long useful = (EPI == EPI_LINEAR && geom.whole_tiles == 0) ? tiles * C::GROUPS : tiles;
     if (PAIR) {
         const long long pairs = useful < sms / 2 ? useful : sms / 2;
         cfg.gridDim = dim3((unsigned)(2 * pairs));
@@ -492,12 +584,17 @@ static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     cfg.blockDim = dim3(THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = stream;
-    CGS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, tmR, bp, rp, op, M, N, K, ldo, ldr));
+    CGS_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmB2, tmO, tmR, bp, rp, op, M, N, K, ldo, ldr, geom));
     return kOk;
 }
 
 // which mainloop: 0 = automatic, 1 = one CTA per tile (M128), 2 = CTA pairs (M256). (tools/kernel_bench.py compares)
 static int g_gemm_force_variant = 0;
+// convolution tiles: 0 = automatic, 1 = never 320-column tiles, 2 = 320-column tiles whenever Cout allows
+static int g_conv_force_wide = 0;
+// (measured, profiles/r02_conv_bench.json: with K = 9 Cin >= 2880 a narrow piece costs nearly a whole tile's time --
+// the k-loop is as long and the operand feed almost the same -- so the convolution keeps its last round whole)
+static int g_conv_whole_tiles = 1;
 
 static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
                        const void* residual, void* out, long long M, int N, int K, long long lda,
@@ -576,12 +673,97 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
     auto bp = static_cast<const __nv_bfloat16*>(bias);
     auto rp = static_cast<const __nv_bfloat16*>(residual);
     auto op = static_cast<__nv_bfloat16*>(out);
+    const ConvGeom none = {};
     if (epi == EPI_GEGLU) {
-        return pair ? launch_variant<EPI_GEGLU, true>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
-                    : launch_variant<EPI_GEGLU, false>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
+        return pair ? launch_variant<EPI_GEGLU, true>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles2, stream)
+                    : launch_variant<EPI_GEGLU, false>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles1, stream);
     }
-    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles2, stream)
-                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, tiles1, stream);
+    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles2, stream)
+                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles1, stream);
+}
+
+// 3x3 / stride 1 / pad 1 convolution over channels-last images as an implicit GEMM (see the CONV notes at the top).
+// x: [n_img, H, W, Cin] with `ldx` elements between consecutive pixels (>= Cin: a channel slice of a wider buffer is
+// fine), w: [Cout, 3, 3, Cin] contiguous (the channels-last storage of a [Cout, Cin, 3, 3] weight), y / residual:
+// [n_img, H, W, Cout] with pixel strides ldy / ldr.
+static int launch_conv3x3(const void* x, const void* w, const void* bias, const void* residual, void* out, int n_img,
+                          int H, int W, int Cin, int Cout, long long ldx, long long ldy, long long ldr,
+                          cudaStream_t stream) {
+    using namespace gemm;
+    if (n_img < 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) {
+        set_last_error("conv3x3: bad sizes n=%d H=%d W=%d Cin=%d Cout=%d", n_img, H, W, Cin, Cout);
+        return kBadArgument;
+    }
+    if (n_img == 0) return kOk;
+    if (Cin % 8 != 0 || Cout % 32 != 0 || ldx % 8 != 0 || ldy % 8 != 0 || (residual && ldr % 8 != 0) || ldx < Cin ||
+        ldy < Cout || (residual && ldr < Cout)) {
+        set_last_error("conv3x3: Cin (%d) and the pixel strides must be multiples of 8, Cout (%d) of 32", Cin, Cout);
+        return kUnsupportedShape;
+    }
+    if ((reinterpret_cast<uintptr_t>(x) & 0xF) || (reinterpret_cast<uintptr_t>(w) & 0xF) ||
+        (reinterpret_cast<uintptr_t>(out) & 0xF) || (reinterpret_cast<uintptr_t>(bias) & 0xF) ||
+        (reinterpret_cast<uintptr_t>(residual) & 0xF)) {
+        set_last_error("conv3x3: pointers must be 16-byte aligned");
+        return kBadArgument;
+    }
+    // a tile's 128 rows: TH x TW pixels, TW the largest power of two dividing W (at most 128)
+    ConvGeom g;
+    g.H = H;
+    g.W = W;
+    g.TW = 1;
+    while (g.TW < BM && W % (g.TW * 2) == 0) g.TW *= 2;
+    g.TH = BM / g.TW;
+    g.tiles_w = W / g.TW;
+    g.tiles_h = (H + g.TH - 1) / g.TH;
+    g.n_img = n_img;
+    g.cin = Cin;
+    g.cblocks = (Cin + BK - 1) / BK;
+    g.whole_tiles = g_conv_whole_tiles;
+    const long long mtiles = (long long)n_img * g.tiles_h * g.tiles_w;       // 128-row tiles
+    if (mtiles * BM > 0x7fffffffLL) {
+        set_last_error("conv3x3: %lld pixel tiles are too many", mtiles);
+        return kUnsupportedShape;
+    }
+    auto img_map = [&](CUtensorMap* tm, const void* base, int channels, long long ld) {
+        const uint64_t dims[4] = {(uint64_t)channels, (uint64_t)W, (uint64_t)H, (uint64_t)n_img};
+        const uint64_t strides[3] = {(uint64_t)ld * 2, (uint64_t)W * ld * 2, (uint64_t)H * W * ld * 2};
+        const uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, 1};
+        return make_tmap_bf16(tm, base, 4, dims, strides, box);
+    };
+    CUtensorMap tmA, tmB, tmB2, tmO, tmR;
+    int rc = img_map(&tmA, x, Cin, ldx);
+    if (rc != kOk) return rc;
+    rc = img_map(&tmO, out, Cout, ldy);
+    if (rc != kOk) return rc;
+    tmR = tmO;
+    if (residual != nullptr) {
+        rc = img_map(&tmR, residual, Cout, ldr);
+        if (rc != kOk) return rc;
+    }
+    const int K = 9 * Cin;
+    {
+        const uint64_t dims[2] = {(uint64_t)K, (uint64_t)Cout};
+        const uint64_t strides[1] = {(uint64_t)K * 2};
+        const uint32_t box[2] = {BK, BN_HALF};
+        rc = make_tmap_bf16(&tmB, w, 2, dims, strides, box);
+        if (rc != kOk) return rc;
+        const uint32_t box2[2] = {BK, B2_ROWS};
+        rc = make_tmap_bf16(&tmB2, w, 2, dims, strides, box2);
+        if (rc != kOk) return rc;
+    }
+    const long long tiles_m = (mtiles + 1) / 2;
+    const int M = (int)(mtiles * BM);
+    auto bp = static_cast<const __nv_bfloat16*>(bias);
+    auto rp = static_cast<const __nv_bfloat16*>(residual);
+    auto op = static_cast<__nv_bfloat16*>(out);
+    bool wide = Cout % WIDE_N == 0 && Cout % UMMA_N != 0;      // 320, 960: tiles of 256 would end in a 64-column one
+    if (g_conv_force_wide == 1) wide = false;
+    if (g_conv_force_wide == 2) wide = Cout % WIDE_N == 0;
+    if (wide)
+        return launch_variant<EPI_LINEAR, true, true, true>(tmA, tmB, tmB2, tmO, tmR, bp, rp, op, M, Cout, K, (int)ldy,
+                                                            (int)ldr, g, tiles_m * (Cout / WIDE_N), stream);
+    return launch_variant<EPI_LINEAR, true, true, false>(tmA, tmB, tmB2, tmO, tmR, bp, rp, op, M, Cout, K, (int)ldy,
+                                                         (int)ldr, g, tiles_m * ((Cout + UMMA_N - 1) / UMMA_N), stream);
 }
 
 }  // namespace cgs
@@ -600,9 +782,25 @@ extern "C" int cgs_linear_fwd(const void* x, const void* w, const void* bias, co
                             ldr, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int cgs_conv3x3_nhwc_fwd(const void* x, const void* w, const void* bias, const void* residual, void* y,
+                                    int n_img, int H, int W, int Cin, int Cout, long long ldx, long long ldy,
+                                    long long ldr, void* stream) {
+    return cgs::launch_conv3x3(x, w, bias, residual, y, n_img, H, W, Cin, Cout, ldx, ldy, ldr,
+                               static_cast<cudaStream_t>(stream));
+}
+
 // Developer switch for the micro-benchmarks: 0 automatic, 1 always one CTA per tile, 2 always CTA pairs. Both
 // mainloops compute the same products in the same order per output element; results are identical.
 extern "C" int cgs_gemm_set_variant(int variant) {
+    // 10 + v: the convolution's tile shape (0 automatic, 1 never 320-column tiles, 2 always when Cout % 320 == 0)
+    if (variant >= 10 && variant <= 12) {
+        cgs::g_conv_force_wide = variant - 10;
+        return cgs::kOk;
+    }
+    if (variant == 20 || variant == 21) {      // 20: the convolution's last round of tiles stays whole (default), 21: pieces
+        cgs::g_conv_whole_tiles = 21 - variant;
+        return cgs::kOk;
+    }
     if (variant < 0 || variant > 2) {
         cgs::set_last_error("gemm_set_variant: %d (0 automatic, 1 single CTA, 2 CTA pairs)", variant);
         return cgs::kBadArgument;

@@ -131,6 +131,38 @@ def conv_nobias(conv, x):
     return conv._conv_forward(x, conv.weight, None)
 
 
+def conv3x3_native_ok(conv, x) -> bool:
+    """The convolution can run on the library's implicit GEMM (cgs_conv3x3_nhwc_fwd): 3x3, stride 1, padding 1,
+    channels-last bf16 input and weight, and an image whose pixel tiles are mostly real pixels."""
+    if not _native.FEATURES["native_conv"]:
+        return False
+    if not (conv.kernel_size == (3, 3) and conv.stride == (1, 1) and conv.padding == (1, 1) and conv.dilation == (1, 1)
+            and conv.groups == 1 and conv.padding_mode == "zeros"):
+        return False
+    cout, cin = conv.weight.shape[:2]
+    if cin % 8 or cout % 32 or x.dim() != 4 or x.shape[1] != cin:
+        return False
+    cl = torch.channels_last
+    if not (x.is_contiguous(memory_format=cl) and conv.weight.is_contiguous(memory_format=cl)):
+        return False
+    if x.shape[1] == 1 or x.stride(1) != 1:          # (size-1 dims make is_contiguous ambiguous)
+        return False
+    return _native.conv3x3_tile_efficiency(x.shape[2], x.shape[3]) >= 0.75
+
+
+def conv3x3(conv, x, bias=None, residual=None):
+    """conv(x) without its own bias, + bias + residual: one launch on the library's implicit GEMM when it can run
+    there, otherwise the bias-free cuDNN convolution followed by the add kernel."""
+    if conv3x3_native_ok(conv, x):
+        return _native.conv3x3(x, conv.weight, bias, residual)
+    y = conv_nobias(conv, x)
+    if residual is not None:
+        return _native.residual_add(residual, y, bias)
+    if bias is not None:
+        y = y + bias.view(1, -1, 1, 1)
+    return y
+
+
 def linear_plain(lin) -> bool:
     return (not lin.comfy_cast_weights and lin.weight_function is None and lin.bias_function is None
             and lin.weight.dtype == ACT_DTYPE)

@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import _native
-from .layers import ORIGINAL, on_fast_device, conv_plain, conv_nobias, groupnorm_apply
+from .layers import ORIGINAL, on_fast_device, conv_plain, conv_nobias, conv3x3, groupnorm_apply
 
 
 # ----------------------------------------------------------------------------------------------
@@ -44,13 +44,25 @@ def resblock_forward(self, x, emb):
     if not _resblock_fast_ok(self, x):
         return ORIGINAL["ResBlock._forward"](self, x, emb)
     conv1, conv2, skip = self.in_layers[2], self.out_layers[3], self.skip_connection
-    h = conv_nobias(conv1, groupnorm_apply(self.in_layers[0], x, silu=True))
+    h = conv3x3(conv1, groupnorm_apply(self.in_layers[0], x, silu=True))
     emb_out = self.emb_layers(emb).type(h.dtype) + conv1.bias            # [N, C]: conv1's bias joins the embedding
     h = groupnorm_apply(self.out_layers[0], h, silu=True, add_nc=emb_out.contiguous())
-    h = conv_nobias(conv2, self.out_layers[2](h))                         # out_layers[2]: Dropout (identity at p = 0)
+    h = self.out_layers[2](h)                                             # Dropout (identity at p = 0)
+    # skip_connection(x) + conv2(h): the biases and the skip image ride in conv2's epilogue (or in the add kernel)
     if isinstance(skip, nn.Identity):
-        return _native.residual_add(x, h, conv2.bias)
-    return _native.residual_add(conv_nobias(skip, x), h, conv2.bias + skip.bias)
+        return conv3x3(conv2, h, conv2.bias, x)
+    return conv3x3(conv2, h, conv2.bias + skip.bias, _skip_conv(skip, x))
+
+
+def _skip_conv(skip, x):
+    """The ResBlock's 1x1 channel-changing skip convolution, bias-free: on channels-last pixels it is a plain GEMM."""
+    cout, cin = skip.weight.shape[:2]
+    if (_native.FEATURES["native_skip"] and skip.kernel_size == (1, 1) and x.is_contiguous(memory_format=torch.channels_last)
+            and x.stride(1) == 1 and cin % 8 == 0 and cout % 32 == 0):
+        n, _, hh, ww = x.shape
+        y = _native.linear(x.permute(0, 2, 3, 1).reshape(n * hh * ww, cin), skip.weight.reshape(cout, cin))
+        return y.view(n, hh, ww, cout).permute(0, 3, 1, 2)
+    return conv_nobias(skip, x)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -71,7 +83,7 @@ def upsample_forward(self, x, output_shape=None, bias_out=None):
     if self.use_conv:
         if bias_out is not None and conv_plain(self.conv):
             bias_out.append(self.conv.bias)
-            return conv_nobias(self.conv, x)
+            return conv3x3(self.conv, x)
         x = self.conv(x)
     return x
 

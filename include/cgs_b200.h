@@ -271,6 +271,24 @@ int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_uncond, const v
 int cgs_gemm_set_variant(int variant);
 
 /*
+ * 3x3 / stride 1 / padding 1 convolution over channels-last bf16 images as an implicit GEMM on the tensor cores, with
+ * bias and a residual image added in the epilogue. Replaces the ResBlock and Upsample convolutions
+ *   h = self.in_layers(x); h = self.out_layers(h); return self.skip_connection(x) + h
+ * (comfy/ldm/modules/diffusionmodules/openaimodel.py:83-96 Upsample.conv, :177-232 ResBlock layers, :235-264
+ * ResBlock._forward; operator class comfy/ops.py:67-80 Conv2d -> F.conv2d), which the reference runs on cuDNN.
+ *   x        [n_img, H, W, Cin]  bf16, `ldx` elements between consecutive pixels (>= Cin; rows and images dense)
+ *   w        [Cout, 3, 3, Cin]   bf16 contiguous: the channels-last storage of the reference's [Cout, Cin, 3, 3] weight
+ *   bias     [Cout] bf16 or NULL; residual [n_img, H, W, Cout] bf16 (pixel stride ldr) or NULL
+ *   y        [n_img, H, W, Cout] bf16, pixel stride ldy; y[p, o] = sum_{r,s,c} x[p + (r-1, s-1), c] * w[o, r, s, c]
+ *            (zero outside the image) + bias[o] + residual[p, o], fp32 accumulation, one rounding to bf16
+ * Cin and the pixel strides must be multiples of 8, Cout of 32. cgs_gemm_set_variant(10 + v) picks the tile shape for
+ * Cout % 320 == 0 (v = 0 automatic, 1 tiles of 256 columns, 2 tiles of 320 columns); results do not depend on it.
+ */
+int cgs_conv3x3_nhwc_fwd(const void* x, const void* w, const void* bias, const void* residual, void* y,
+                         int n_img, int H, int W, int Cin, int Cout, long long ldx, long long ldy, long long ldr,
+                         void* stream);
+
+/*
  * The same tail for a cond / uncond pair that is split across two GPUs (multi-GPU placement):
  * the exchange of the two halves of the model output and cfg_function + sampler update (comfy/samplers.py:234-247,
  * comfy/k_diffusion/sampling.py:137-143, 583-592) in ONE launch, instead of a collective followed by the tail.

@@ -70,6 +70,13 @@ def linear(x: Tensor, w: Tensor, b: Optional[Tensor] = None) -> Tensor:
     return y if b is None else y + b.float()
 
 
+def conv3x3(x: Tensor, w: Tensor, b: Optional[Tensor] = None, residual: Optional[Tensor] = None) -> Tensor:
+    """ops.Conv2d -> F.conv2d with kernel 3, stride 1, padding 1 (comfy/ops.py:67-80), as the ResBlock / Upsample use
+    it (openaimodel.py:83-96, 177-232), plus ResBlock._forward's `skip_connection(x) + h` (:264)."""
+    y = F.conv2d(x.float(), w.float(), None if b is None else b.float(), padding=1)
+    return y if residual is None else y + residual.float()
+
+
 def geglu(x: Tensor, w: Tensor, b: Tensor) -> Tensor:
     """GEGLU.forward: proj -> chunk(2) -> first half * gelu(second half) (attention.py:61-63)."""
     h = linear(x, w, b)

@@ -95,6 +95,12 @@ def linear(x, weight, bias=None, residual=None, out=None):
     return y
 
 
+def conv3x3(x, weight, bias=None, residual=None):
+    _count("conv3x3")
+    y = F.conv2d(x, weight, bias, padding=1)
+    return y if residual is None else y + residual
+
+
 def unet_input(x, sigma, copies, sigma_data=1.0):
     _count("unet_input")
     s = sigma.view(-1, *([1] * (x.dim() - 1)))
@@ -147,7 +153,7 @@ def patched():
     """Swap the stand-ins into _native and point layers.py at (cpu, fp32)."""
     from comfy_gen_server_b200 import _native, layers
     names = ["attention", "layer_norm", "add_layer_norm_", "group_norm", "residual_add", "cat_channels",
-             "upsample_nearest2x", "transpose_add", "geglu", "linear", "unet_input", "cfg_denoise",
+             "upsample_nearest2x", "transpose_add", "geglu", "linear", "conv3x3", "unet_input", "cfg_denoise",
              "sampler_step_euler", "sampler_step_dpmpp2m", "cfg_sampler_tail"]
     saved = {n: getattr(_native, n) for n in names}
     saved_layers = (layers.ACT_DTYPE, layers.DEVICE_TYPE)

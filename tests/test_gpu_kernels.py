@@ -414,6 +414,68 @@ def test_linear_vs_oracle(M, K, Nn, res):
     assert (y - ref).abs().max() <= ulp_tol(ref)
 
 
+# ------------------------------------------------------------------------------------------ 3x3 convolution
+CONV_SHAPES = [
+    # n, H, W, Cin, Cout, bias, residual
+    (2, 16, 16, 64, 64, True, False),         # 8 x 16 pixel tiles
+    (1, 32, 32, 320, 320, True, True),        # one 320-column tile (two MMAs per k-step), residual in the epilogue
+    (2, 8, 8, 128, 640, False, True),         # tile taller than the image (TW 8, TH 16)
+    (1, 24, 24, 64, 96, True, False),         # W = 24: TW 8, TH 16, the second tile row half outside; Cout = 96
+    (3, 12, 20, 72, 32, True, True),          # W = 20: TW 4, TH 32; Cin not a multiple of 64 (partial channel block)
+    (1, 128, 128, 64, 320, True, False),      # one image row per tile
+    (1, 8, 48, 64, 64, False, False),         # three pixel tiles: the last pair's second CTA has none
+    (1, 64, 64, 960, 320, True, True),        # SDXL output-block shape (960 -> 320), K = 8640
+    (2, 32, 32, 640, 1280, True, False),      # five tile columns
+    (1, 16, 16, 64, 960, True, True),         # Cout = 960: three 320-column tiles
+]
+
+
+@pytest.mark.parametrize("n,H,W,Cin,Cout,use_b,use_r", CONV_SHAPES)
+def test_conv3x3_vs_oracle(n, H, W, Cin, Cout, use_b, use_r):
+    """cgs_conv3x3_nhwc_fwd against F.conv2d in fp32 (the reference's operator, comfy/ops.py:67-80)."""
+    cl = torch.channels_last
+    x = bf(randn((n, Cin, H, W), 1)).contiguous(memory_format=cl)
+    w = bf(randn((Cout, Cin, 3, 3), 2, (9 * Cin) ** -0.5)).contiguous(memory_format=cl)
+    b = bf(randn((Cout,), 3, 0.1)) if use_b else None
+    r = bf(randn((n, Cout, H, W), 4)).contiguous(memory_format=cl) if use_r else None
+    y = N().conv3x3(x, w, b, r)
+    assert y.shape == (n, Cout, H, W) and y.is_contiguous(memory_format=cl)
+    ref = O.conv3x3(x.cpu(), w.cpu(), None if b is None else b.cpu(), None if r is None else r.cpu())
+    assert (y.float().cpu() - ref).abs().max() <= ulp_tol(ref)
+
+
+def test_conv3x3_channel_slice_and_tile_shapes():
+    """The input may be a channel slice of a wider channels-last buffer, and the two tilings of Cout = 320 / 640
+    (256-column tiles, 320-column tiles) give bit-identical results."""
+    cl = torch.channels_last
+    n = N()
+    big = bf(randn((2, 192, 16, 32), 1)).contiguous(memory_format=cl)
+    x = big[:, 64:128]
+    for cout in (320, 640):
+        w = bf(randn((cout, 64, 3, 3), 2, 24 ** -1.0)).contiguous(memory_format=cl)
+        b = bf(randn((cout,), 3, 0.1))
+        ref = O.conv3x3(x.cpu(), w.cpu(), b.cpu())
+        outs = []
+        for v in (11, 12, 10):
+            assert n.load_library().cgs_gemm_set_variant(v) == 0
+            outs.append(n.conv3x3(x, w, b))
+        assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+        assert (outs[0].float().cpu() - ref).abs().max() <= ulp_tol(ref)
+
+
+def test_conv3x3_errors():
+    n = N()
+    cl = torch.channels_last
+    w = bf(randn((64, 64, 3, 3), 2)).contiguous(memory_format=cl)
+    with pytest.raises(RuntimeError):
+        n.conv3x3(bf(randn((1, 64, 8, 8), 1)), w)                                   # NCHW input
+    with pytest.raises(RuntimeError):
+        n.conv3x3(bf(randn((1, 64, 8, 8), 1)).contiguous(memory_format=cl), bf(randn((64, 64, 3, 3), 2)))   # NCHW weight
+    with pytest.raises(RuntimeError):
+        n.conv3x3(bf(randn((1, 60, 8, 8), 1)).contiguous(memory_format=cl),
+                  bf(randn((64, 60, 3, 3), 2)).contiguous(memory_format=cl))        # Cin % 8
+
+
 def test_gemm_errors():
     n = N()
     with pytest.raises(RuntimeError):

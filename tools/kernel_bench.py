@@ -80,34 +80,6 @@ def bench_gemm_variants():
     shapes = [("geglu", "sdxl_L2", 16 * 1024, 1280, 5120), ("geglu", "sdxl_L1", 16 * 4096, 640, 2560),
               ("linear", "sdxl_L2_ff_out", 16 * 1024, 5120, 1280), ("linear", "sdxl_L1_ff_out", 16 * 4096, 2560, 640),
               ("linear", "sdxl_L2_to_q", 16 * 1024, 1280, 1280), ("linear", "sdxl_L1_to_q", 16 * 4096, 640, 640),
-              ("linear", "sdxl_L2_qkv", 16 * 1024, 1280, 3840), ("linear", "sdxl_L2_ff_out_b1", 2 * 1024, 5120, 1280),
-              ("geglu", "sdxl_L2_b1", 2 * 1024, 1280, 5120)]
-    for kind, label, M, K, Nn in shapes:
-        row = {"kernel": "gemm_variants", "kind": kind, "case": label, "M": M, "K": K, "N": Nn}
-        if kind == "geglu":
-            x, w, b = rnd((M, K)), rnd((2 * Nn, K), scale=K ** -0.5), rnd((2 * Nn,), scale=0.1)
-            fn = lambda: N.geglu(x, w, b)
-            flops = 2.0 * M * K * 2 * Nn
-        else:
-            x, w, b = rnd((M, K)), rnd((Nn, K), scale=K ** -0.5), rnd((Nn,), scale=0.1)
-            fn = lambda: N.linear(x, w, b)
-            flops = 2.0 * M * K * Nn
-            row["cublaslt_tflops"] = flops / timeit(lambda: torch.nn.functional.linear(x, w, b)) / 1e9
-        for v, name in ((1, "single_cta"), (2, "cta_pair"), (0, "auto")):
-            lib.cgs_gemm_set_variant(v)
-            row[name + "_tflops"] = flops / timeit(fn) / 1e9
-        lib.cgs_gemm_set_variant(0)
-        out.append(row)
-    return out
-
-
-def bench_gemm_variants():
-    """one CTA per tile vs CTA pairs (cgs_gemm_set_variant) vs cuBLASLt, on the SDXL GEMM shapes"""
-    out = []
-    lib = N.load_library()
-    shapes = [("geglu", "sdxl_L2", 16 * 1024, 1280, 5120), ("geglu", "sdxl_L1", 16 * 4096, 640, 2560),
-              ("linear", "sdxl_L2_ff_out", 16 * 1024, 5120, 1280), ("linear", "sdxl_L1_ff_out", 16 * 4096, 2560, 640),
-              ("linear", "sdxl_L2_to_q", 16 * 1024, 1280, 1280), ("linear", "sdxl_L1_to_q", 16 * 4096, 640, 640),
               ("linear", "sdxl_L2_qkv", 16 * 1024, 1280, 3840), ("linear", "sdxl_L1_qkv", 16 * 4096, 640, 1920),
               ("linear", "sdxl_L2_ff_out_b1", 2 * 1024, 5120, 1280), ("linear", "sdxl_L2_to_q_b1", 2 * 1024, 1280, 1280),
               ("linear", "sdxl_L2_qkv_b1", 2 * 1024, 1280, 3840), ("geglu", "sdxl_L2_b1", 2 * 1024, 1280, 5120)]
@@ -126,6 +98,49 @@ def bench_gemm_variants():
             lib.cgs_gemm_set_variant(v)
             row[name + "_tflops"] = round(flops / timeit(fn) / 1e9, 1)
         lib.cgs_gemm_set_variant(0)
+        out.append(row)
+    return out
+
+
+def bench_conv():
+    """3x3 convolutions of the SDXL UNet (channels-last, UNet batch 16 and 2) against cuDNN (F.conv2d)"""
+    out = []
+    lib = N.load_library()
+    cl = torch.channels_last
+    # (label, n, hw, Cin, Cout)
+    cases = [("L0_320_320", 16, 128, 320, 320), ("L0_960_320", 16, 128, 960, 320), ("L0_640_320", 16, 128, 640, 320),
+             ("L1_640_640", 16, 64, 640, 640), ("L1_320_640", 16, 64, 320, 640), ("L1_1920_640", 16, 64, 1920, 640),
+             ("L1_1280_640", 16, 64, 1280, 640), ("L1_960_640", 16, 64, 960, 640),
+             ("L2_1280_1280", 16, 32, 1280, 1280), ("L2_640_1280", 16, 32, 640, 1280), ("L2_2560_1280", 16, 32, 2560, 1280),
+             ("L2_1920_1280", 16, 32, 1920, 1280), ("UP_1280_1280", 16, 64, 1280, 1280), ("UP_640_640", 16, 128, 640, 640),
+             ("b1_L0_320_320", 2, 128, 320, 320), ("b1_L1_640_640", 2, 64, 640, 640), ("b1_L2_1280_1280", 2, 32, 1280, 1280),
+             ("b1_L2_2560_1280", 2, 32, 2560, 1280)]
+    only = os.environ.get("CONV_CASES")
+    for label, n, hw, cin, cout in cases:
+        if only and not any(label.startswith(o) for o in only.split(",")):
+            continue
+        x = rnd((n, cin, hw, hw)).contiguous(memory_format=cl)
+        w = rnd((cout, cin, 3, 3), scale=(9 * cin) ** -0.5).contiguous(memory_format=cl)
+        b = rnd((cout,), scale=0.1)
+        r = rnd((n, cout, hw, hw)).contiguous(memory_format=cl)
+        flops = 2.0 * n * hw * hw * 9 * cin * cout
+        row = {"kernel": "conv3x3", "case": label, "n": n, "hw": hw, "cin": cin, "cout": cout}
+        row["cudnn_nobias_tflops"] = round(flops / timeit(lambda: torch.nn.functional.conv2d(x, w, None, padding=1)) / 1e9, 1)
+        row["cudnn_bias_tflops"] = round(flops / timeit(lambda: torch.nn.functional.conv2d(x, w, b, padding=1)) / 1e9, 1)
+        variants = ((11, "tiles256"), (12, "tiles320")) if cout % 320 == 0 else ((10, "tiles256"),)
+        nores = bool(os.environ.get("CONV_NORES"))          # (variant builds without the residual stage)
+        for v, name in variants:
+            lib.cgs_gemm_set_variant(v)
+            for sv, sname in ((20, ""), (21, "_pieces")):
+                lib.cgs_gemm_set_variant(sv)
+                row[name + sname + "_tflops"] = round(flops / timeit(lambda: N.conv3x3(x, w, b)) / 1e9, 1)
+                if not nores:
+                    row[name + sname + "_residual_tflops"] = round(flops / timeit(lambda: N.conv3x3(x, w, b, r)) / 1e9, 1)
+        lib.cgs_gemm_set_variant(10)
+        lib.cgs_gemm_set_variant(20)
+        y = N.conv3x3(x, w, b)
+        ref = torch.nn.functional.conv2d(x, w, b, padding=1)
+        row["max_abs_vs_cudnn"] = float((y.float() - ref.float()).abs().max())
         out.append(row)
     return out
 
@@ -203,7 +218,7 @@ def bench_tail():
 
 def main():
     which = sys.argv[1:] or ["attn", "geglu", "linear", "ln", "tail"]
-    fns = {"gemmv": bench_gemm_variants, "attn": bench_attn, "geglu": bench_geglu, "linear": bench_linear, "ln": bench_ln, "tail": bench_tail}
+    fns = {"conv": bench_conv, "gemmv": bench_gemm_variants, "attn": bench_attn, "geglu": bench_geglu, "linear": bench_linear, "ln": bench_ln, "tail": bench_tail}
     results = []
     for w in which:
         for r in fns[w]():
