@@ -266,7 +266,7 @@ def run_ours(args):
 
     integration.install()
     if args.native is not None:         # A/B: which of the block's projections run on the library GEMM
-        for f in ("qkv", "to_out", "ff_out", "conv", "skip"):
+        for f in ("qkv", "to_out", "ff_out", "conv", "skip", "upconv"):
             _native.FEATURES["native_" + f] = f in args.native.split(",")
 
     # ---- device-resident leg: K denoise steps through the fused step of the drop-in --------------

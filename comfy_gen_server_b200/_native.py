@@ -38,6 +38,7 @@ _SIGNATURES = {
     "cgs_linear_fwd": [_c_void_p] * 5 + [_c_ll, _c_int, _c_int, _c_ll, _c_ll, _c_ll, _c_ll, _c_void_p],
     "cgs_gemm_set_variant": [_c_int],
     "cgs_conv3x3_nhwc_fwd": [_c_void_p] * 5 + [_c_int] * 5 + [_c_ll] * 3 + [_c_void_p],
+    "cgs_upsample2x_conv3x3_nhwc_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 2 + [_c_void_p],
     "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
     "cgs_cfg_denoise_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                               _c_ll, _c_ll, _c_void_p],
@@ -324,7 +325,8 @@ FEATURES = {"residual_add": True, "cat_channels": True, "upsample2x": True, "fol
             "native_qkv": False, "native_to_out": True, "native_ff_out": True,
             # 3x3 convolutions of the ResBlocks / Upsample on this library's implicit GEMM instead of cuDNN
             # (native_skip: the ResBlock's 1x1 skip convolution as a plain GEMM over the pixel rows)
-            "native_conv": True, "native_skip": False}
+            # (native_upconv: Upsample's interpolate + conv as four 2x2 convolutions of the small image)
+            "native_conv": True, "native_skip": False, "native_upconv": True}
 
 
 def _same_dense_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
@@ -525,6 +527,48 @@ def conv3x3(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] 
                                                  bias.data_ptr() if bias is not None else None, r_ptr, out.data_ptr(),
                                                  n, h, w, cin, cout, sw if n else cin, cout, cout, _stream(x))
     _check(rc, "cgs_conv3x3_nhwc_fwd")
+    return out
+
+
+def upsample2x_conv_weights(weight: torch.Tensor) -> torch.Tensor:
+    """[Cout, Cin, 3, 3] -> the pre-summed phase weights [4, Cout, 2, 2, Cin] of cgs_upsample2x_conv3x3_nhwc_fwd
+    (include/cgs_b200.h): phase (a, b) adds up the 3x3 taps that read the same input pixel."""
+    w = weight.float()
+    rows = (torch.stack([w[:, :, 0], w[:, :, 1] + w[:, :, 2]], dim=2),          # a = 0: {0}, {1, 2}
+            torch.stack([w[:, :, 0] + w[:, :, 1], w[:, :, 2]], dim=2))          # a = 1: {0, 1}, {2}
+    phases = []
+    for ra in rows:                                                              # ra: [Cout, Cin, 2, 3]
+        cols = (torch.stack([ra[..., 0], ra[..., 1] + ra[..., 2]], dim=3),
+                torch.stack([ra[..., 0] + ra[..., 1], ra[..., 2]], dim=3))
+        phases += [c.permute(0, 2, 3, 1) for c in cols]                          # [Cout, 2, 2, Cin]
+    return torch.stack(phases).to(weight.dtype).contiguous()
+
+
+def upsample2x_conv3x3(x: torch.Tensor, w4: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """F.conv2d(F.interpolate(x, scale_factor=2, mode="nearest"), weight, bias, padding=1) for channels-last bf16
+    images, as four 2 x 2 convolutions of x (w4 = upsample2x_conv_weights(weight)); the up-sampled image is never
+    formed."""
+    _require_cuda("upsample2x_conv3x3 x", x, torch.bfloat16)
+    _require_cuda("upsample2x_conv3x3 w4", w4, torch.bfloat16)
+    if x.dim() != 4 or w4.dim() != 5 or tuple(w4.shape[0:1] + w4.shape[2:4]) != (4, 2, 2) or w4.shape[4] != x.shape[1] \
+            or not w4.is_contiguous():
+        raise RuntimeError(f"upsample2x_conv3x3: x {tuple(x.shape)} / w4 {tuple(w4.shape)}")
+    n, cin, h, w = x.shape
+    cout = w4.shape[1]
+    sn, sc, sh, sw = x.stride()
+    if n and not (sc == 1 and sh == w * sw and (n == 1 or sn == h * w * sw)):
+        raise RuntimeError(f"upsample2x_conv3x3: x must be channels-last with dense pixels (strides {x.stride()})")
+    out = torch.empty((n, cout, 2 * h, 2 * w), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    if bias is not None:
+        _require_cuda("upsample2x_conv3x3 bias", bias, torch.bfloat16)
+        if bias.numel() != cout or not bias.is_contiguous():
+            raise RuntimeError("upsample2x_conv3x3: bias must be contiguous [Cout]")
+    with _Launch("conv3x3", x, 2.0 * n * h * w * 16 * cin * cout, n=4):
+        rc = load_library().cgs_upsample2x_conv3x3_nhwc_fwd(x.data_ptr(), w4.data_ptr(),
+                                                            bias.data_ptr() if bias is not None else None,
+                                                            out.data_ptr(), n, h, w, cin, cout, sw if n else cin, cout,
+                                                            _stream(x))
+    _check(rc, "cgs_upsample2x_conv3x3_nhwc_fwd")
     return out
 
 

@@ -88,6 +88,8 @@ constexpr int B2_BYTES = B2_ROWS * BK * 2;    // 4 KiB
 // a tile's rows as a rectangle of pixels (CONV)
 struct ConvGeom {
     int H, W, TH, TW, tiles_h, tiles_w, n_img, cin, cblocks;
+    int taps, taps_w;     // filter taps (9 / 3 for 3x3; 4 / 2 for one phase of the 2x-upsample convolution)
+    int off_h, off_w;     // input pixel of tap (0, 0) relative to the output pixel (-1, -1 for 3x3 / pad 1)
     int whole_tiles;      // != 0: the last round is not dealt out in column pieces (measurement switch)
 };
 
@@ -248,7 +250,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int workers = PAIR ? (gridDim.x >> 1) : gridDim.x;
     const int tiles_m = (M + C::TILE_M - 1) / C::TILE_M;
     const int tiles_n = (EPI == EPI_GEGLU) ? (N / BN_HALF) : ((N + TILE_N - 1) / TILE_N);
-    const int kblocks = CONV ? 9 * geom.cblocks : (K + BK - 1) / BK;
+    const int kblocks = CONV ? geom.taps * geom.cblocks : (K + BK - 1) / BK;
     const Schedule<EPI, TILE_N> sched(workers, tiles_m, tiles_n, N, geom.whole_tiles == 0);
     const int n_items = sched.items(worker);
 
@@ -319,8 +321,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                             mbar_expect_tx(&full[stage], 2 * (A_BYTES + BN_HALF * BK * 2 + (wide_piece ? B2_BYTES : 0)));
                         int kcoord = kb * BK;
                         if (CONV) {
-                            const int r = tap / 3, sft = tap - 3 * r;
-                            tma_load_4d_pair(sa, &tmA, &full[stage], cb * BK, w0 + sft - 1, h0 + r - 1, img);
+                            const int r = tap / geom.taps_w, sft = tap - geom.taps_w * r;
+                            tma_load_4d_pair(sa, &tmA, &full[stage], cb * BK, w0 + sft + geom.off_w, h0 + r + geom.off_h,
+                                             img);
                             kcoord = tap * geom.cin + cb * BK;
                             if (++cb == geom.cblocks) { cb = 0; ++tap; }
                         } else {
@@ -682,28 +685,34 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
                 : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles1, stream);
 }
 
-// 3x3 / stride 1 / pad 1 convolution over channels-last images as an implicit GEMM (see the CONV notes at the top).
+// Convolution over channels-last images as an implicit GEMM (see the CONV notes at the top): taps_h x taps_w filter
+// taps, tap (0, 0) reading the input pixel (off_h, off_w) away from the output pixel, zero outside the image.
 // x: [n_img, H, W, Cin] with `ldx` elements between consecutive pixels (>= Cin: a channel slice of a wider buffer is
-// fine), w: [Cout, 3, 3, Cin] contiguous (the channels-last storage of a [Cout, Cin, 3, 3] weight), y / residual:
-// [n_img, H, W, Cout] with pixel strides ldy / ldr.
-static int launch_conv3x3(const void* x, const void* w, const void* bias, const void* residual, void* out, int n_img,
-                          int H, int W, int Cin, int Cout, long long ldx, long long ldy, long long ldr,
-                          cudaStream_t stream) {
+// fine), w: [Cout, taps_h, taps_w, Cin] contiguous. Output / residual pixel (n, h, w) lives at
+// base + n * s[2] + h * s[1] + w * s[0] elements -- dense images, or one phase of a 2x finer lattice.
+struct ImgStrides {
+    long long s[3];
+};
+
+static int launch_conv(const char* who, const void* x, const void* w, const void* bias, const void* residual, void* out,
+                       int n_img, int H, int W, int Cin, int Cout, int taps_h, int taps_w, int off_h, int off_w,
+                       long long ldx, ImgStrides so, ImgStrides sr, cudaStream_t stream) {
     using namespace gemm;
     if (n_img < 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) {
-        set_last_error("conv3x3: bad sizes n=%d H=%d W=%d Cin=%d Cout=%d", n_img, H, W, Cin, Cout);
+        set_last_error("%s: bad sizes n=%d H=%d W=%d Cin=%d Cout=%d", who, n_img, H, W, Cin, Cout);
         return kBadArgument;
     }
     if (n_img == 0) return kOk;
-    if (Cin % 8 != 0 || Cout % 32 != 0 || ldx % 8 != 0 || ldy % 8 != 0 || (residual && ldr % 8 != 0) || ldx < Cin ||
-        ldy < Cout || (residual && ldr < Cout)) {
-        set_last_error("conv3x3: Cin (%d) and the pixel strides must be multiples of 8, Cout (%d) of 32", Cin, Cout);
+    bool ok = Cin % 8 == 0 && Cout % 32 == 0 && ldx % 8 == 0 && ldx >= Cin;
+    for (int i = 0; i < 3; ++i) ok = ok && so.s[i] % 8 == 0 && (!residual || sr.s[i] % 8 == 0);
+    if (!ok) {
+        set_last_error("%s: Cin (%d) and the pixel strides must be multiples of 8, Cout (%d) of 32", who, Cin, Cout);
         return kUnsupportedShape;
     }
     if ((reinterpret_cast<uintptr_t>(x) & 0xF) || (reinterpret_cast<uintptr_t>(w) & 0xF) ||
         (reinterpret_cast<uintptr_t>(out) & 0xF) || (reinterpret_cast<uintptr_t>(bias) & 0xF) ||
         (reinterpret_cast<uintptr_t>(residual) & 0xF)) {
-        set_last_error("conv3x3: pointers must be 16-byte aligned");
+        set_last_error("%s: pointers must be 16-byte aligned", who);
         return kBadArgument;
     }
     // a tile's 128 rows: TH x TW pixels, TW the largest power of two dividing W (at most 128)
@@ -718,29 +727,35 @@ static int launch_conv3x3(const void* x, const void* w, const void* bias, const 
     g.n_img = n_img;
     g.cin = Cin;
     g.cblocks = (Cin + BK - 1) / BK;
+    g.taps = taps_h * taps_w;
+    g.taps_w = taps_w;
+    g.off_h = off_h;
+    g.off_w = off_w;
     g.whole_tiles = g_conv_whole_tiles;
     const long long mtiles = (long long)n_img * g.tiles_h * g.tiles_w;       // 128-row tiles
     if (mtiles * BM > 0x7fffffffLL) {
-        set_last_error("conv3x3: %lld pixel tiles are too many", mtiles);
+        set_last_error("%s: %lld pixel tiles are too many", who, mtiles);
         return kUnsupportedShape;
     }
-    auto img_map = [&](CUtensorMap* tm, const void* base, int channels, long long ld) {
+    auto img_map = [&](CUtensorMap* tm, const void* base, int channels, const long long* st) {
         const uint64_t dims[4] = {(uint64_t)channels, (uint64_t)W, (uint64_t)H, (uint64_t)n_img};
-        const uint64_t strides[3] = {(uint64_t)ld * 2, (uint64_t)W * ld * 2, (uint64_t)H * W * ld * 2};
+        const uint64_t strides[3] = {(uint64_t)st[0] * 2, (uint64_t)st[1] * 2, (uint64_t)st[2] * 2};
         const uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, 1};
         return make_tmap_bf16(tm, base, 4, dims, strides, box);
     };
     CUtensorMap tmA, tmB, tmB2, tmO, tmR;
-    int rc = img_map(&tmA, x, Cin, ldx);
+    const long long sx[3] = {ldx, (long long)W * ldx, (long long)H * W * ldx};
+    int rc = img_map(&tmA, x, Cin, sx);
     if (rc != kOk) return rc;
-    rc = img_map(&tmO, out, Cout, ldy);
+    rc = img_map(&tmO, out, Cout, so.s);
     if (rc != kOk) return rc;
     tmR = tmO;
     if (residual != nullptr) {
-        rc = img_map(&tmR, residual, Cout, ldr);
+        rc = img_map(&tmR, residual, Cout, sr.s);
         if (rc != kOk) return rc;
     }
-    const int K = 9 * Cin;
+    const int K = g.taps * Cin;
+    const long long ldy = so.s[0], ldr = sr.s[0];
     {
         const uint64_t dims[2] = {(uint64_t)K, (uint64_t)Cout};
         const uint64_t strides[1] = {(uint64_t)K * 2};
@@ -785,8 +800,39 @@ extern "C" int cgs_linear_fwd(const void* x, const void* w, const void* bias, co
 extern "C" int cgs_conv3x3_nhwc_fwd(const void* x, const void* w, const void* bias, const void* residual, void* y,
                                     int n_img, int H, int W, int Cin, int Cout, long long ldx, long long ldy,
                                     long long ldr, void* stream) {
-    return cgs::launch_conv3x3(x, w, bias, residual, y, n_img, H, W, Cin, Cout, ldx, ldy, ldr,
-                               static_cast<cudaStream_t>(stream));
+    if (ldy < Cout || (residual && ldr < Cout)) {
+        cgs::set_last_error("conv3x3: pixel strides of y / residual are smaller than Cout");
+        return cgs::kBadArgument;
+    }
+    const cgs::ImgStrides so = {{ldy, (long long)W * ldy, (long long)H * W * ldy}};
+    const cgs::ImgStrides sr = {{ldr, (long long)W * ldr, (long long)H * W * ldr}};
+    return cgs::launch_conv("conv3x3", x, w, bias, residual, y, n_img, H, W, Cin, Cout, 3, 3, -1, -1, ldx, so, sr,
+                            static_cast<cudaStream_t>(stream));
+}
+
+// conv3x3(nearest-neighbour 2x up-sampling of x) without the up-sampled image: output pixel (2i + a, 2j + b) sees
+// only 2 x 2 distinct input pixels, so each of the four phases (a, b) is a 2 x 2 convolution of x with the 3x3 taps
+// that fall on the same input pixel added up -- 16 instead of 36 multiply-adds per input pixel, channel pair and
+// output, and no 4x larger intermediate. w4: [4 phases (a * 2 + b)][Cout][2][2][Cin], see cgs_b200.h.
+extern "C" int cgs_upsample2x_conv3x3_nhwc_fwd(const void* x, const void* w4, const void* bias, void* y, int n_img,
+                                               int H, int W, int Cin, int Cout, long long ldx, long long ldy,
+                                               void* stream) {
+    if (ldy < Cout) {
+        cgs::set_last_error("upsample2x_conv3x3: pixel stride of y is smaller than Cout");
+        return cgs::kBadArgument;
+    }
+    const long long W2 = 2LL * W, H2 = 2LL * H;
+    const cgs::ImgStrides so = {{2 * ldy, 2 * W2 * ldy, H2 * W2 * ldy}};
+    for (int a = 0; a < 2; ++a) {
+        for (int b = 0; b < 2; ++b) {
+            const auto* wp = static_cast<const __nv_bfloat16*>(w4) + (size_t)(a * 2 + b) * Cout * 4 * Cin;
+            auto* yp = static_cast<__nv_bfloat16*>(y) + (a * W2 + b) * ldy;
+            const int rc = cgs::launch_conv("upsample2x_conv3x3", x, wp, bias, nullptr, yp, n_img, H, W, Cin, Cout, 2, 2,
+                                            a - 1, b - 1, ldx, so, so, static_cast<cudaStream_t>(stream));
+            if (rc != cgs::kOk) return rc;
+        }
+    }
+    return cgs::kOk;
 }
 
 // Developer switch for the micro-benchmarks: 0 automatic, 1 always one CTA per tile, 2 always CTA pairs. Both

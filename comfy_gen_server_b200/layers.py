@@ -163,6 +163,19 @@ def conv3x3(conv, x, bias=None, residual=None):
     return y
 
 
+def upsample2x_conv3x3(conv, x):
+    """conv(interpolate(x, 2x nearest)) without the conv's bias, or None when it cannot run on the library's kernel.
+    The pre-summed phase weights are derived once per weight tensor and kept on the module."""
+    if not (_native.FEATURES["native_upconv"] and conv3x3_native_ok(conv, x)):
+        return None
+    key = (conv.weight.data_ptr(), conv.weight._version)
+    cached = conv.__dict__.get("_cgs_upconv")
+    if cached is None or cached[0] != key:
+        cached = (key, _native.upsample2x_conv_weights(conv.weight))
+        conv.__dict__["_cgs_upconv"] = cached
+    return _native.upsample2x_conv3x3(x, cached[1])
+
+
 def linear_plain(lin) -> bool:
     return (not lin.comfy_cast_weights and lin.weight_function is None and lin.bias_function is None
             and lin.weight.dtype == ACT_DTYPE)

@@ -21,7 +21,8 @@ import torch
 import torch.nn as nn
 
 from . import _native
-from .layers import ORIGINAL, on_fast_device, conv_plain, conv_nobias, conv3x3, groupnorm_apply
+from .layers import (ORIGINAL, on_fast_device, conv_plain, conv_nobias, conv3x3, upsample2x_conv3x3,
+                     groupnorm_apply)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -77,6 +78,11 @@ def upsample_forward(self, x, output_shape=None, bias_out=None):
     if output_shape is not None:
         shape = [output_shape[2], output_shape[3]]
     if shape == [x.shape[2] * 2, x.shape[3] * 2]:
+        if self.use_conv and bias_out is not None and conv_plain(self.conv):
+            y = upsample2x_conv3x3(self.conv, x)          # interpolate + conv in one go, on the small image
+            if y is not None:
+                bias_out.append(self.conv.bias)
+                return y
         x = _native.upsample_nearest2x(x)
     else:
         x = torch.nn.functional.interpolate(x, size=shape, mode="nearest")

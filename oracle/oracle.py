@@ -77,6 +77,11 @@ def conv3x3(x: Tensor, w: Tensor, b: Optional[Tensor] = None, residual: Optional
     return y if residual is None else y + residual.float()
 
 
+def upsample2x_conv3x3(x: Tensor, w: Tensor, b: Optional[Tensor] = None) -> Tensor:
+    """Upsample.forward with use_conv (openaimodel.py:83-96): nearest 2x interpolation, then the 3x3 convolution."""
+    return conv3x3(F.interpolate(x.float(), scale_factor=2, mode="nearest"), w, b)
+
+
 def geglu(x: Tensor, w: Tensor, b: Tensor) -> Tensor:
     """GEGLU.forward: proj -> chunk(2) -> first half * gelu(second half) (attention.py:61-63)."""
     h = linear(x, w, b)

@@ -336,3 +336,24 @@ def test_reference_param_shapes_match_unet_config(reference_tree):
     from comfy_gen_server_b200 import models
     for fam in ("tiny_sd15", "tiny_sd21v", "tiny_sdxl"):
         models.build_model(fam, "cpu", seed=1, dtype=torch.float32)
+
+
+def test_upsample_conv_phase_weights_are_the_same_convolution():
+    """The algebra behind cgs_upsample2x_conv3x3_nhwc_fwd, checked on the CPU in float64: conv3x3(nearest 2x(x)) ==
+    the four 2x2 phase convolutions of x with the pre-summed weights, interleaved."""
+    import torch.nn.functional as F
+    from comfy_gen_server_b200 import _native
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(2, 5, 6, 7, generator=g, dtype=torch.float64)
+    w = torch.randn(4, 5, 3, 3, generator=g, dtype=torch.float64)
+    ref = F.conv2d(F.interpolate(x, scale_factor=2, mode="nearest"), w, padding=1)
+    w4 = _native.upsample2x_conv_weights(w)                      # [4, Cout, 2, 2, Cin]
+    assert w4.shape == (4, 4, 2, 2, 5)
+    out = torch.zeros_like(ref)
+    for a in range(2):
+        for b in range(2):
+            k = w4[a * 2 + b].permute(0, 3, 1, 2).double()       # [Cout, Cin, 2, 2]
+            # tap (dr, ds) reads input pixel (i + a - 1 + dr, j + b - 1 + ds): pad so that index 0 is offset a - 1
+            xp = F.pad(x, (1 - b, b, 1 - a, a))
+            out[:, :, a::2, b::2] = F.conv2d(xp, k)
+    assert (out - ref).abs().max() < 1e-5          # (the weights are summed in fp32)

@@ -463,6 +463,22 @@ def test_conv3x3_channel_slice_and_tile_shapes():
         assert (outs[0].float().cpu() - ref).abs().max() <= ulp_tol(ref)
 
 
+@pytest.mark.parametrize("n,H,W,Cin,Cout,use_b", [(1, 16, 16, 64, 64, True), (2, 8, 32, 128, 320, False),
+                                                   (1, 32, 32, 640, 640, True), (2, 12, 20, 72, 96, True),
+                                                   (1, 64, 64, 64, 1280, True)])
+def test_upsample2x_conv3x3_vs_oracle(n, H, W, Cin, Cout, use_b):
+    """cgs_upsample2x_conv3x3_nhwc_fwd (four 2x2 phase convolutions of the small image) against the reference's
+    interpolate -> conv2d (openaimodel.py:83-96) in fp32."""
+    cl = torch.channels_last
+    x = bf(randn((n, Cin, H, W), 1)).contiguous(memory_format=cl)
+    w = bf(randn((Cout, Cin, 3, 3), 2, (9 * Cin) ** -0.5)).contiguous(memory_format=cl)
+    b = bf(randn((Cout,), 3, 0.1)) if use_b else None
+    y = N().upsample2x_conv3x3(x, N().upsample2x_conv_weights(w), b)
+    assert y.shape == (n, Cout, 2 * H, 2 * W) and y.is_contiguous(memory_format=cl)
+    ref = O.upsample2x_conv3x3(x.cpu(), w.cpu(), None if b is None else b.cpu())
+    assert (y.float().cpu() - ref).abs().max() <= ulp_tol(ref)
+
+
 def test_conv3x3_errors():
     n = N()
     cl = torch.channels_last

@@ -138,6 +138,13 @@ def bench_conv():
                     row[name + sname + "_residual_tflops"] = round(flops / timeit(lambda: N.conv3x3(x, w, b, r)) / 1e9, 1)
         lib.cgs_gemm_set_variant(10)
         lib.cgs_gemm_set_variant(20)
+        if label.startswith("UP_"):      # Upsample: interpolate + conv; here on the half-size image, as four 2x2 convolutions
+            xs = rnd((n, cin, hw // 2, hw // 2)).contiguous(memory_format=cl)
+            w4 = N.upsample2x_conv_weights(w)
+            ms = timeit(lambda: N.upsample2x_conv3x3(xs, w4, b))
+            ms_ref = timeit(lambda: torch.nn.functional.conv2d(N.upsample_nearest2x(xs), w, None, padding=1))
+            row["upconv_ms"], row["upsample_kernel_plus_cudnn_ms"] = round(ms, 4), round(ms_ref, 4)
+            row["upconv_equiv_tflops"] = round(flops / ms / 1e9, 1)
         y = N.conv3x3(x, w, b)
         ref = torch.nn.functional.conv2d(x, w, b, padding=1)
         row["max_abs_vs_cudnn"] = float((y.float() - ref.float()).abs().max())
