@@ -123,7 +123,7 @@ groupnorm_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __res
 //             (sample, chunk, group) in a small global scratch buffer;
 //   kernel 2  every CTA first adds up its sample's partials (L2-resident, a few KB), then normalises its chunk.
 // Thread <-> channel mapping is fixed (a thread always owns the same 8 channels), so gamma/beta/group ids live in
-// registers; a vector of 8 channels straddles at most two groups (cpg >= 8).
+// registers; a vector of 8 channels straddles at most two groups (cpg >= 8, or cpg == 4: exactly two).
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kGnMaxGroups = 32;
 
@@ -370,8 +370,10 @@ extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const v
         return kBadArgument;
     }
     if (N == 0) return kOk;
-    if (C % 8 != 0 || C / groups < 8 || groups > kGnMaxGroups || C / 8 > 320) {
-        set_last_error("groupnorm_nhwc: C=%d groups=%d unsupported (C %% 8 == 0, C/groups >= 8, groups <= 32, C <= 2560)",
+    // a 16-byte vector of 8 channels may touch at most two groups: 8 or more channels per group, or exactly 4
+    const int cpg_ = groups > 0 ? C / groups : 0;
+    if (C % 8 != 0 || (cpg_ < 8 && cpg_ != 4) || groups > kGnMaxGroups || C / 8 > 320) {
+        set_last_error("groupnorm_nhwc: C=%d groups=%d unsupported (C %% 8 == 0, C/groups >= 8 or == 4, groups <= 32, C <= 2560)",
                        C, groups);
         return kUnsupportedShape;
     }

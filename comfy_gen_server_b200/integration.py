@@ -84,11 +84,12 @@ def install(bf16_unet: bool = True) -> List[str]:
     _rebind(ref_unet.UNetModel, "forward", unet_path.unet_forward, log, "UNetModel.forward")
     # model wrapper: sigma scaling + cast and eps / v -> denoised as one kernel each (model_base.py:74-98)
     _rebind(ref_mb.BaseModel, "apply_model", guider.apply_model_forward, log, "BaseModel.apply_model")
-    # VAE decode (diffusionmodules/model.py:139-160, 281-294): GroupNorm + SiLU and the residual adds on the kernels
+    # VAE decode (diffusionmodules/model.py:48-75, 139-160, 281-294): GroupNorm + SiLU, the 3x3 convolutions, up-sampling
     import comfy.ldm.modules.diffusionmodules.model as ref_vae
     from . import vae_path
     _rebind(ref_vae.ResnetBlock, "forward", vae_path.resnet_forward, log, "vae.ResnetBlock.forward")
     _rebind(ref_vae.AttnBlock, "forward", vae_path.attn_forward, log, "vae.AttnBlock.forward")
+    _rebind(ref_vae.Upsample, "forward", vae_path.upsample_forward, log, "vae.Upsample.forward")
     # sampler functions: looked up with getattr(k_diffusion_sampling, "sample_" + name) (samplers.py:556); they
     # reach the fused CFG + update step (guider.FusedDenoise) through the guider behind the model they are given
     _rebind(ref_kd, "sample_euler", sampling.sample_euler, log, "sample_euler")

@@ -78,7 +78,8 @@ def groupnorm_kernel_ok(self, input) -> bool:
     if input.is_contiguous():                                       # NCHW kernel
         return (input.shape[2] * input.shape[3]) % 8 == 0
     if input.is_contiguous(memory_format=torch.channels_last):      # NHWC kernels
-        return c % 8 == 0 and c // self.num_groups >= 8 and self.num_groups <= 32 and c <= 2560
+        cpg = c // self.num_groups
+        return c % 8 == 0 and c % self.num_groups == 0 and (cpg >= 8 or cpg == 4) and self.num_groups <= 32 and c <= 2560
     return False
 
 
@@ -154,6 +155,8 @@ def conv3x3(conv, x, bias=None, residual=None):
     """conv(x) without its own bias, + bias + residual: one launch on the library's implicit GEMM when it can run
     there, otherwise the bias-free cuDNN convolution followed by the add kernel."""
     if conv3x3_native_ok(conv, x):
+        if residual is not None:
+            residual = residual.contiguous(memory_format=torch.channels_last)
         return _native.conv3x3(x, conv.weight, bias, residual)
     y = conv_nobias(conv, x)
     if residual is not None:
@@ -163,8 +166,8 @@ def conv3x3(conv, x, bias=None, residual=None):
     return y
 
 
-def upsample2x_conv3x3(conv, x):
-    """conv(interpolate(x, 2x nearest)) without the conv's bias, or None when it cannot run on the library's kernel.
+def upsample2x_conv3x3(conv, x, bias=None):
+    """conv(interpolate(x, 2x nearest)) (+ bias, not the conv's own), or None when it cannot run on the library's kernel.
     The pre-summed phase weights are derived once per weight tensor and kept on the module."""
     if not (_native.FEATURES["native_upconv"] and conv3x3_native_ok(conv, x)):
         return None
@@ -173,7 +176,7 @@ def upsample2x_conv3x3(conv, x):
     if cached is None or cached[0] != key:
         cached = (key, _native.upsample2x_conv_weights(conv.weight))
         conv.__dict__["_cgs_upconv"] = cached
-    return _native.upsample2x_conv3x3(x, cached[1])
+    return _native.upsample2x_conv3x3(x, cached[1], bias)
 
 
 def linear_plain(lin) -> bool:

@@ -121,7 +121,8 @@ def _ensure_channels_last_weights(unet) -> None:
     patch replaced since): cuDNN then needs no per-call weight transform."""
     for p in unet.parameters():
         if p.dim() == 4 and not p.is_contiguous(memory_format=torch.channels_last):
-            p.data = p.data.contiguous(memory_format=torch.channels_last)
+            with torch.inference_mode(False):        # the parameter must stay usable outside inference mode
+                p.data = p.data.contiguous(memory_format=torch.channels_last)
 
 
 def _run_block(seq, x, emb, context, transformer_options, output_shape, up_bias, ref):

@@ -244,7 +244,10 @@ def test_groupnorm_with_channel_addend():
 @pytest.mark.parametrize("N_,C,H,W,silu,add", [(2, 320, 32, 32, True, True), (2, 640, 16, 16, True, False),
                                                (1, 1280, 8, 8, False, False), (3, 960, 12, 12, True, True),
                                                (2, 2560, 16, 16, True, False), (1, 256, 3, 5, True, True),
-                                               (2, 1920, 32, 32, True, True)])
+                                               (2, 1920, 32, 32, True, True),
+                                               # the VAE decoder's levels: 4 / 8 / 16 channels per group
+                                               (1, 128, 64, 64, True, False), (2, 256, 24, 24, True, False),
+                                               (1, 512, 16, 16, False, False)])
 def test_groupnorm_channels_last_vs_oracle(N_, C, H, W, silu, add):
     x = bf(randn((N_, C, H, W), 1, 2.0) + 0.5).contiguous(memory_format=torch.channels_last)
     e = bf(randn((N_, C), 4)) if add else None
