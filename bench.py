@@ -359,6 +359,7 @@ def run_ours(args):
         ln_ms, ln_bytes, ln_n = family_pass("add_layernorm", min(args.steps, 3))
         pln_ms, pln_bytes, pln_n = family_pass("layernorm", min(args.steps, 3))
         lin_ms, lin_flops, lin_n = family_pass("linear", min(args.steps, 3))
+        conv_ms, conv_flops, conv_n = family_pass("conv3x3", min(args.steps, 3))
 
         # ---- end-to-end leg: public API, pinned host buffers -> final latents on the host -------
         noise_h, latent_h = noise.pin_memory(), latent.pin_memory()
@@ -442,6 +443,14 @@ def run_ours(args):
                                 "peak": peak_tf, "unit": "TFLOP/s", "launches_timed": lin_n,
                                 "frac": (lin_flops / (lin_ms * 1e-3) / 1e12 / peak_tf) if lin_ms > 0 else 0.0,
                                 "ms_in_kernel_per_step": lin_ms / min(args.steps, 3)},
+            "roofline_conv": {"kernel": "gemm_kernel<EPI_LINEAR, PAIR, CONV> (cgs_conv3x3_nhwc_fwd, "
+                                        "cgs_upsample2x_conv3x3_nhwc_fwd: ResBlock / Upsample convolutions)",
+                              "bound": "tensor", "achieved": conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0,
+                              "peak": peak_tf, "unit": "TFLOP/s", "launches_timed": conv_n,
+                              "frac": (conv_flops / (conv_ms * 1e-3) / 1e12 / peak_tf) if conv_ms > 0 else 0.0,
+                              "ms_in_kernel_per_step": conv_ms / min(args.steps, 3),
+                              "note": "algorithmic FLOPs of the kernel as run: 2 x pixels x 9 Cin x Cout, and "
+                                      "2 x small-image pixels x 16 Cin x Cout for interpolate + conv"},
             "roofline_layernorm": {"kernel": "layernorm_stream_kernel (cgs_layernorm_fwd)", "bound": "hbm",
                                    "achieved": plnbw, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                    "frac": plnbw / peaks["hbm_gbs"], "launches_timed": pln_n,

@@ -140,9 +140,12 @@ static GnNhwcGeom gn_nhwc_geom(int N, int C, int HW) {
     g.nvec = C / 8;
     g.rows_per_iter = g.nvec >= 256 ? 1 : 256 / g.nvec;
     g.threads = g.nvec * g.rows_per_iter;
-    // enough CTAs to fill the GPU a few times over, but no more than 128 partials per sample
+    // enough CTAs to fill the GPU a few times over. Up to 128 partials per sample the normalise kernel adds them up
+    // itself; beyond that (one or two large images: the VAE decoder) a small kernel in between does it once --
+    // 128 CTAs for a 268 MB image ran the pair of kernels at a third of the HBM bandwidth.
     int want = (sm_count() * 4 + N - 1) / (N > 0 ? N : 1);
-    if (want > 128) want = 128;
+    const int cap = (long long)HW * C * 2 >= (64LL << 20) ? 1024 : 128;      // (per sample: 64 MB and more)
+    if (want > cap) want = cap;
     if (want < 1) want = 1;
     int rows = (HW + want - 1) / want;
     rows = ((rows + g.rows_per_iter - 1) / g.rows_per_iter) * g.rows_per_iter;
@@ -241,14 +244,42 @@ gn_nhwc_stats_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
     }
 }
 
+// (more than 128 chunks per sample) adds up a sample's partials once, in a fixed order: final[n][g] = (sum, sum sq)
+__global__ void __launch_bounds__(256)
+gn_nhwc_finalize_kernel(const float* __restrict__ partial, float* __restrict__ final_, int chunks, int groups) {
+    __shared__ float red[256][2];
+    const int n = blockIdx.x;
+    const int g = threadIdx.x % groups, stripe = threadIdx.x / groups, stripes = blockDim.x / groups;
+    float s = 0.f, q = 0.f;
+    if (stripe < stripes) {
+        const float* src = partial + ((size_t)n * chunks * groups + g) * 2;
+        for (int k = stripe; k < chunks; k += stripes) {
+            s += src[(size_t)k * groups * 2];
+            q += src[(size_t)k * groups * 2 + 1];
+        }
+    }
+    red[threadIdx.x][0] = s;
+    red[threadIdx.x][1] = q;
+    __syncthreads();
+    if (threadIdx.x < groups) {
+        s = q = 0.f;
+        for (int k = 0; k < stripes; ++k) {
+            s += red[k * groups + g][0];
+            q += red[k * groups + g][1];
+        }
+        final_[((size_t)n * groups + g) * 2] = s;
+        final_[((size_t)n * groups + g) * 2 + 1] = q;
+    }
+}
+
 template <bool SILU>
 __global__ void __launch_bounds__(320)
 gn_nhwc_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ add_nc,
                      const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
-                     const float* __restrict__ partial, __nv_bfloat16* __restrict__ y, int C, int HW, int groups,
-                     int nvec, int rows_per_iter, int rows_per_chunk, float eps) {
+                     const float* __restrict__ partial, int chunks, __nv_bfloat16* __restrict__ y, int C, int HW,
+                     int groups, int nvec, int rows_per_iter, int rows_per_chunk, float eps) {
     __shared__ float stat[kGnMaxGroups][2];    // mean, rstd
-    const int n = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x;
+    const int n = blockIdx.y, chunk = blockIdx.x;    // `chunks` partials per sample (1 after the finalize kernel)
     const int cpg = C / groups;
     if (threadIdx.x < groups) {
         float s = 0.f, q = 0.f;
@@ -358,7 +389,7 @@ extern "C" int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* 
 extern "C" long long cgs_groupnorm_nhwc_scratch_bytes(int N, int C, int HW, int groups) {
     if (N <= 0 || C <= 0 || HW <= 0 || groups <= 0) return 0;
     const cgs::GnNhwcGeom g = cgs::gn_nhwc_geom(N, C, HW);
-    return (long long)N * g.chunks * groups * 2 * (long long)sizeof(float);
+    return (long long)N * (g.chunks + 1) * groups * 2 * (long long)sizeof(float);      // partials + their sums
 }
 
 extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
@@ -382,7 +413,7 @@ extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const v
         return kUnsupportedShape;
     }
     const GnNhwcGeom g = gn_nhwc_geom(N, C, HW);
-    const long long need = (long long)N * g.chunks * groups * 2 * (long long)sizeof(float);
+    const long long need = (long long)N * (g.chunks + 1) * groups * 2 * (long long)sizeof(float);
     if (scratch == nullptr || scratch_bytes < need) {
         set_last_error("groupnorm_nhwc: scratch buffer of %lld bytes needed (got %lld)", need, scratch_bytes);
         return kScratchTooSmall;
@@ -398,12 +429,21 @@ extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const v
     gn_nhwc_stats_kernel<<<grid, g.threads, 0, st>>>(xp, ap, sp, C, HW, groups, g.nvec, g.rows_per_iter,
                                                      g.rows_per_chunk);
     CGS_CUDA_CHECK(cudaGetLastError());
+    const float* stats = sp;
+    int stat_chunks = g.chunks;
+    if (g.chunks > 128) {
+        float* fin = sp + (size_t)N * g.chunks * groups * 2;
+        gn_nhwc_finalize_kernel<<<N, 256, 0, st>>>(sp, fin, g.chunks, groups);
+        CGS_CUDA_CHECK(cudaGetLastError());
+        stats = fin;
+        stat_chunks = 1;
+    }
     if (silu)
-        gn_nhwc_apply_kernel<true><<<grid, g.threads, 0, st>>>(xp, ap, gp, bp, sp, yp, C, HW, groups, g.nvec,
-                                                               g.rows_per_iter, g.rows_per_chunk, eps);
+        gn_nhwc_apply_kernel<true><<<grid, g.threads, 0, st>>>(xp, ap, gp, bp, stats, stat_chunks, yp, C, HW, groups,
+                                                               g.nvec, g.rows_per_iter, g.rows_per_chunk, eps);
     else
-        gn_nhwc_apply_kernel<false><<<grid, g.threads, 0, st>>>(xp, ap, gp, bp, sp, yp, C, HW, groups, g.nvec,
-                                                                g.rows_per_iter, g.rows_per_chunk, eps);
+        gn_nhwc_apply_kernel<false><<<grid, g.threads, 0, st>>>(xp, ap, gp, bp, stats, stat_chunks, yp, C, HW, groups,
+                                                                g.nvec, g.rows_per_iter, g.rows_per_chunk, eps);
     CGS_CUDA_CHECK(cudaGetLastError());
     return kOk;
 }

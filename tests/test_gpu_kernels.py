@@ -247,7 +247,9 @@ def test_groupnorm_with_channel_addend():
                                                (2, 1920, 32, 32, True, True),
                                                # the VAE decoder's levels: 4 / 8 / 16 channels per group
                                                (1, 128, 64, 64, True, False), (2, 256, 24, 24, True, False),
-                                               (1, 512, 16, 16, False, False)])
+                                               (1, 512, 16, 16, False, False),
+                                               # 64 MB per sample: more than 128 partials, summed by the kernel in between
+                                               (1, 128, 512, 512, True, False)])
 def test_groupnorm_channels_last_vs_oracle(N_, C, H, W, silu, add):
     x = bf(randn((N_, C, H, W), 1, 2.0) + 0.5).contiguous(memory_format=torch.channels_last)
     e = bf(randn((N_, C), 4)) if add else None

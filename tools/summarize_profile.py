@@ -8,10 +8,12 @@ tag = sys.argv[1]
 
 # the first launches of the timed step (level-1 SpatialTransformer of SDXL at 1024^2, B2 = 16): what each capture is
 SHAPES = [
-    ("gemm_kernel<1, 0>", "GEGLU GEMM (one CTA per tile) M=65536 K=640 N=2560 (2N=5120)", 425984000, 429496729600.0),
-    ("gemm_kernel<1, 1>", "GEGLU GEMM (CTA pairs) M=16384 K=1280 N=5120 (2N=10240)", 236060672, 429496729600.0),
-    ("gemm_kernel<0, 0>", "linear + bias + residual (one CTA per tile) to_out M=65536 K=640 N=640", 252477440, 53687091200.0),
-    ("gemm_kernel<0, 1>", "linear + bias + residual (CTA pairs): first captured = ff.net.2 level 1 M=65536 K=2560 N=640", 506593280, 214748364800.0),
+    ("gemm_kernel<1, 0, 0, 0>", "GEGLU GEMM (one CTA per tile) M=65536 K=640 N=2560 (2N=5120)", 425984000, 429496729600.0),
+    ("gemm_kernel<1, 1, 0, 0>", "GEGLU GEMM (CTA pairs) M=16384 K=1280 N=5120 (2N=10240)", 236060672, 429496729600.0),
+    ("gemm_kernel<0, 0, 0, 0>", "linear + bias + residual (one CTA per tile) to_out M=65536 K=640 N=640", 252477440, 53687091200.0),
+    ("gemm_kernel<0, 1, 0, 0>", "linear + bias + residual (CTA pairs): first captured = ff.net.2 level 1 M=65536 K=2560 N=640", 506593280, 214748364800.0),
+    ("gemm_kernel<0, 1, 1, 1>", "3x3 convolution, 320-column tiles: first captured = 16 x 128^2, 320 -> 320", 337387520, 483183820800.0),
+    ("gemm_kernel<0, 1, 1, 0>", "3x3 convolution, 256-column tiles: first captured = 16 x 32^2, 640 -> 1280", 77660160, 241591910400.0),
     ("attn_fwd_kernel<1, 3, 4", "self-attention B2=16 H=10 N=4096 d=64", 335544320, 687194767360.0),
     ("attn_fwd_kernel<1, 1, 1, 96", "cross-attention B2=16 H=10 Nq=4096 Nk=77 d=64 (96-key tile)", 170926080, 12918456320.0),
     ("layernorm_stream_kernel<3, 16>", "LayerNorm 65536 x 640", 167772160, 0.0),
@@ -59,7 +61,11 @@ def launches():
 
 def full():
     rep = os.path.join(ROOT, "gpurun_out", "prof_top.ncu-rep")
-    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    raw = os.path.join(ROOT, "gpurun_out", "prof_top_raw.csv")        # exported on the GPU box by tools/profile_step.sh
+    if os.path.exists(raw):
+        txt = open(raw).read()
+    else:
+        txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(txt)))
     hdr = rows[0]
     want = {"gpu__time_duration.sum": "ms_under_ncu", "dram__bytes_read.sum": "dram_read_bytes",
@@ -101,7 +107,7 @@ def full():
                 k.update({"shape": shape, "algorithmic_bytes": abytes, "algorithmic_flops": aflops})
         kernels.append(k)
     out = {"source": "ncu --set full --clock-control none --import-source on --profile-from-start off -k "
-                     "regex:'gemm_kernel|attn_fwd_kernel|layernorm_stream' -c 16 python bench.py --steps 1 --warmup 3 --profile "
+                     "regex:'gemm_kernel|attn_fwd_kernel|layernorm_stream' -c 48 python bench.py --steps 1 --warmup 3 --profile "
                      "(gpurun, B200; report gpurun_out/prof_top.ncu-rep, not committed)",
            "note": "first launches of the timed step = SDXL level-1 SpatialTransformer (B2 = 16, 4096 tokens, C = 640); one "
                    "entry per distinct kernel / grid", "kernels": kernels}
