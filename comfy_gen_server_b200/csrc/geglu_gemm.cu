@@ -68,6 +68,17 @@
 
 namespace cgs {
 
+// -DCGS_GEMM_TRACE: clock stamps of CTA 0's MMA thread and first epilogue warp, per work item (tools/gemm_trace.py)
+#ifdef CGS_GEMM_TRACE
+__device__ long long* g_gemm_trace = nullptr;
+#define GEMM_STAMP(item, slot)                                                                        \
+    do {                                                                                              \
+        if (g_gemm_trace != nullptr && blockIdx.x == 0 && (item) < 32) g_gemm_trace[(item) * 16 + (slot)] = clock64(); \
+    } while (0)
+#else
+#define GEMM_STAMP(item, slot) do { } while (0)
+#endif
+
 namespace gemm {
 constexpr int BM = 128;                       // rows per CTA
 constexpr int BK = 64;
@@ -362,12 +373,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 const bool wide_piece = WIDE && pc.width > UMMA_N;
                 const uint32_t idesc = umma_idesc_bf16(C::TILE_M, wide_piece ? UMMA_N : pc.width, 0);
                 const uint32_t idesc2 = umma_idesc_bf16(C::TILE_M, WIDE_N - UMMA_N, 0);
+                GEMM_STAMP(i, 0);
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
+                GEMM_STAMP(i, 1);
                 const uint32_t d_tmem = tmem_base + acc * UMMA_N;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
+                    if (kb == 0) GEMM_STAMP(i, 2);
                     const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
                     const uint64_t adesc = umma_desc_sw128(sa, 16, 1024);
                     const uint64_t bdesc = umma_desc_sw128(sa + A_BYTES, 16, 1024);
@@ -389,6 +403,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 if (PAIR) tc_commit_pair(&tfull[acc]); else tc_commit(&tfull[acc]);
+                GEMM_STAMP(i, 3);
                 if (WIDE) acc_phase ^= 1;                       // one accumulator buffer
                 else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
@@ -445,8 +460,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (CONV) conv_tile(geom, mb * 2 + (int)rank, img, h0, w0);
             // (the previous item's last residual reads are behind its second named barrier: the tile is free)
             if (use_res && store_leader) load_residual(col_base, pc.width, row_base);
+            if (store_leader) GEMM_STAMP(i, 4);
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
+            if (store_leader) GEMM_STAMP(i, 5);
             const uint32_t taddr = tmem_base + acc * UMMA_N + (static_cast<uint32_t>(quad * 32) << 16);
             const int PASSES = (EPI == EPI_GEGLU) ? 1 : (pc.width + 127) / 128;
 #pragma unroll 1
@@ -489,6 +506,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     uint32_t v[32];
                     tmem_ld_x32(taddr + pass * 128 + cg * 32, v);
                     tmem_wait_ld();
+                    if (store_leader) GEMM_STAMP(i, 6 + pass);
                     if (pass == PASSES - 1) release_acc(acc);
                     // widths are multiples of 32: a 32-column group is all in or all out of the piece
                     const bool col_ok = pass * 128 + cg * 32 < pc.width;
@@ -544,6 +562,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     tma_store_commit();
                 }
             }
+            if (store_leader) GEMM_STAMP(i, 10);
             if (WIDE) acc_phase ^= 1;
             else if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
@@ -834,6 +853,13 @@ extern "C" int cgs_upsample2x_conv3x3_nhwc_fwd(const void* x, const void* w4, co
     }
     return cgs::kOk;
 }
+
+#ifdef CGS_GEMM_TRACE
+extern "C" int cgs_gemm_set_trace(void* buf) {
+    long long* p = static_cast<long long*>(buf);
+    return cudaMemcpyToSymbol(cgs::g_gemm_trace, &p, sizeof(p)) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 // Developer switch for the micro-benchmarks: 0 automatic, 1 always one CTA per tile, 2 always CTA pairs. Both
 // mainloops compute the same products in the same order per output element; results are identical.

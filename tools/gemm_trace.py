@@ -1,0 +1,27 @@
+"""Timeline of CTA 0 of the convolution GEMM (clock64 stamps per work item; tracing build only):
+   python -c "from comfy_gen_server_b200 import build as b; b.build_variant('build_variants/libcgs_gemm_trace.so', ['-DCGS_GEMM_TRACE'], ['geglu_gemm.cu'])"
+   CGS_LIB=build_variants/libcgs_gemm_trace.so python tools/gemm_trace.py"""
+import ctypes, os, sys, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from comfy_gen_server_b200 import _native as N
+N._lib = N.load_library(os.path.join(ROOT, os.environ["CGS_LIB"]))
+lib = N._lib
+cl = torch.channels_last
+buf = torch.zeros(32 * 16, dtype=torch.int64, device="cuda")
+lib.cgs_gemm_set_trace.argtypes = [ctypes.c_void_p]
+for n, hw, cin, cout in [(16, 128, 320, 320), (16, 64, 640, 640), (16, 32, 1280, 1280)]:
+    x = torch.randn(n, cin, hw, hw, device="cuda").bfloat16().contiguous(memory_format=cl)
+    w = (torch.randn(cout, cin, 3, 3, device="cuda") * (9 * cin) ** -0.5).bfloat16().contiguous(memory_format=cl)
+    b = torch.randn(cout, device="cuda").bfloat16()
+    for _ in range(3):
+        buf.zero_()
+        assert lib.cgs_gemm_set_trace(buf.data_ptr()) == 0
+        N.conv3x3(x, w, b)
+    torch.cuda.synchronize()
+    t = buf.cpu().view(32, 16)
+    t0 = int(t[0, 0])
+    print(f"conv {cin}->{cout} @ {hw}^2: item | mma: wait_tempty tempty_ok first_full last_commit | epi: wait_tfull tfull_ok ld0 ld1 ld2 item_end   (clocks since the first stamp)")
+    for i in range(0, 6):
+        row = [(int(v) - t0) if v > 0 else -1 for v in t[i, :11]]
+        print(f"  {i:2d} | " + " ".join(f"{v:8d}" for v in row[:4]) + " | " + " ".join(f"{v:8d}" for v in row[4:11]))
