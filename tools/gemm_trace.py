@@ -25,6 +25,8 @@ for n, hw, cin, cout in [(16, 128, 320, 320), (16, 64, 640, 640), (16, 32, 1280,
     for i in range(0, 6):
         row = [(int(v) - t0) if v > 0 else -1 for v in t[i, :11]]
         print(f"  {i:2d} | " + " ".join(f"{v:8d}" for v in row[:4]) + " | " + " ".join(f"{v:8d}" for v in row[4:11]))
+        p0 = [(int(v) - int(t[i, 6])) if v > 0 else -1 for v in t[i, 11:16]]
+        print("       pass 0 after its tcgen05.ld: computed, store-read waited, barrier 1, tile written, barrier 2: " + " ".join(f"{v:6d}" for v in p0))
 
 for M, K, Nn, res in [(16384, 1280, 1280, True), (16384, 1280, 1280, False), (16384, 5120, 1280, True), (65536, 640, 640, True)]:
     x = torch.randn(M, K, device="cuda").bfloat16()
@@ -45,3 +47,5 @@ for M, K, Nn, res in [(16384, 1280, 1280, True), (16384, 1280, 1280, False), (16
     for i in range(0, 7):
         row = [(int(v) - t0) if v > 0 else -1 for v in t[i, :11]]
         print(f"  {i:2d} | " + " ".join(f"{v:8d}" for v in row[:4]) + " | " + " ".join(f"{v:8d}" for v in row[4:11]))
+        p0 = [(int(v) - int(t[i, 6])) if v > 0 else -1 for v in t[i, 11:16]]
+        print("       pass 0 after its tcgen05.ld: computed, store-read waited, barrier 1, tile written, barrier 2: " + " ".join(f"{v:6d}" for v in p0))
