@@ -265,6 +265,9 @@ def run_ours(args):
                             f"same schedule, batch and inputs, CUDA events around the call (incl. its per-step syncs)"}
 
     integration.install()
+    if args.gemm_set:
+        for code in args.gemm_set.split(","):
+            assert _native.load_library().cgs_gemm_set_variant(int(code)) == 0, code
     if args.native is not None:         # A/B: which of the block's projections run on the library GEMM
         for f in ("qkv", "to_out", "ff_out", "conv", "skip", "upconv"):
             _native.FEATURES["native_" + f] = f in args.native.split(",")
@@ -493,6 +496,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-library-baseline", action="store_true")
     ap.add_argument("--native", default=None, help="A/B: comma list of qkv,to_out,ff_out,conv,skip on the library GEMM")
+    ap.add_argument("--gemm-set", default=None, help="A/B: comma list of cgs_gemm_set_variant codes (include/cgs_b200.h)")
     ap.add_argument("--profile", action="store_true",
                     help="only the timed denoise steps, bracketed by cudaProfilerStart/Stop (for ncu)")
     args = ap.parse_args()

@@ -101,7 +101,8 @@ struct ConvGeom {
     int H, W, TH, TW, tiles_h, tiles_w, n_img, cin, cblocks;
     int taps, taps_w;     // filter taps (9 / 3 for 3x3; 4 / 2 for one phase of the 2x-upsample convolution)
     int off_h, off_w;     // input pixel of tap (0, 0) relative to the output pixel (-1, -1 for 3x3 / pad 1)
-    int whole_tiles;      // != 0: the last round is not dealt out in column pieces (measurement switch)
+    int whole_tiles;      // last, partly filled round of tiles: 0 = 64-column groups dealt out evenly, 1 = whole tiles,
+                          // 2 = halves or quarters of a tile, at most one per worker (Schedule)
 };
 
 template <bool PAIR, int EPI, bool WIDE = false>
@@ -164,13 +165,22 @@ struct Schedule {
     static constexpr int G = TILE_N / 64;
     int workers, num_tiles, tiles_m, tiles_n, N, full_rounds, rem, active, groups;
     bool split;
-    __device__ Schedule(int workers_, int tiles_m_, int tiles_n_, int N_, bool split_ = true)
+    int gpt, gw;          // (mode 2) pieces per tile of the last round (1, 2 or 4) and their width
+    // mode 2: a narrow piece is not proportionally cheaper than a tile (same A traffic, same k-loop), so a worker
+    // with two of them is the slowest of the round. Halve or quarter the tiles only as far as every worker still gets
+    // at most one piece; otherwise keep them whole.
+    __device__ Schedule(int workers_, int tiles_m_, int tiles_n_, int N_, int mode = 0)
         : workers(workers_), num_tiles(tiles_m_ * tiles_n_), tiles_m(tiles_m_), tiles_n(tiles_n_), N(N_),
-          split(split_ && EPI == gemm::EPI_LINEAR) {
+          split(mode != 1 && EPI == gemm::EPI_LINEAR), gpt(0), gw(TILE_N) {
         full_rounds = num_tiles / workers;
         rem = num_tiles - full_rounds * workers;
         groups = rem * G;
         active = split ? (groups < workers ? groups : workers) : rem;
+        if (split && mode == 2) {
+            gpt = (TILE_N % 256 == 0 && rem * 4 <= workers) ? 4 : (TILE_N % 128 == 0 && rem * 2 <= workers) ? 2 : 1;
+            gw = TILE_N / gpt;
+            active = rem * gpt;
+        }
     }
     __device__ int tile_width(int tile) const {
         if (EPI == gemm::EPI_GEGLU) return gemm::UMMA_N;
@@ -181,7 +191,7 @@ struct Schedule {
     }
     __device__ int items(int w) const {
         if (w >= active) return full_rounds;
-        if (!split) return full_rounds + 1;
+        if (!split || gpt > 0) return full_rounds + 1;
         const int a = (int)((long long)groups * w / active), b = (int)((long long)groups * (w + 1) / active);
         return full_rounds + ((b - 1) / G - a / G) + 1;
     }
@@ -196,6 +206,14 @@ struct Schedule {
         if (!split) {
             p.tile = full_rounds * workers + w;
             p.width = tile_width(p.tile);
+            return p;
+        }
+        if (gpt > 0) {
+            p.tile = full_rounds * workers + w / gpt;
+            p.n_off = (w % gpt) * gw;
+            const int have = tile_width(p.tile) - p.n_off;
+            p.width = have < gw ? have : gw;
+            if (p.width < 0) p.width = 0;
             return p;
         }
         const int a = (int)((long long)groups * w / active), b = (int)((long long)groups * (w + 1) / active);
@@ -262,7 +280,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int tiles_m = (M + C::TILE_M - 1) / C::TILE_M;
     const int tiles_n = (EPI == EPI_GEGLU) ? (N / BN_HALF) : ((N + TILE_N - 1) / TILE_N);
     const int kblocks = CONV ? geom.taps * geom.cblocks : (K + BK - 1) / BK;
-    const Schedule<EPI, TILE_N> sched(workers, tiles_m, tiles_n, N, geom.whole_tiles == 0);
+    const Schedule<EPI, TILE_N> sched(workers, tiles_m, tiles_n, N, geom.whole_tiles);
     const int n_items = sched.items(worker);
 
     if (warp == 0 && elect_one()) {
@@ -321,6 +339,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 const int row0 = (EPI == EPI_GEGLU) ? nb * BN_HALF : nb * TILE_N + pc.n_off;
                 const int row1 = (EPI == EPI_GEGLU) ? N + nb * BN_HALF : row0 + (PAIR ? w1 / 2 : BN_HALF);
                 const bool two_boxes = PAIR || pc.width > BN_HALF;
+                // (pairs, EPI_LINEAR) a piece narrower than 256 columns stages only the B rows it needs
+                const int b_boxes = (w1 / 2 + B2_ROWS - 1) / B2_ROWS;
+                const bool narrow_b = PAIR && EPI == EPI_LINEAR && w1 < UMMA_N;
                 int tap = 0, cb = 0;                       // (CONV) filter tap 0..8 and 64-channel block inside it
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
@@ -329,7 +350,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if (PAIR) {
                         // both CTAs' bytes are credited to the leader's barrier; the leader announces them
                         if (rank == 0)
-                            mbar_expect_tx(&full[stage], 2 * (A_BYTES + BN_HALF * BK * 2 + (wide_piece ? B2_BYTES : 0)));
+                            mbar_expect_tx(&full[stage], 2 * (A_BYTES + (narrow_b ? b_boxes * B2_BYTES : BN_HALF * BK * 2) +
+                                                              (wide_piece ? B2_BYTES : 0)));
                         int kcoord = kb * BK;
                         if (CONV) {
                             const int r = tap / geom.taps_w, sft = tap - geom.taps_w * r;
@@ -340,7 +362,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                         } else {
                             tma_load_2d_pair(sa, &tmA, &full[stage], kcoord, m0);
                         }
-                        tma_load_2d_pair(sb, &tmB, &full[stage], kcoord, rank == 0 ? row0 : row1);
+                        if (narrow_b) {              // w1 / 2 rows as 32-row boxes (the 128-row box costs a full tile's feed)
+                            for (int bx = 0; bx < b_boxes; ++bx)
+                                tma_load_2d_pair(sb + bx * B2_BYTES, &tmB2, &full[stage], kcoord,
+                                                 (rank == 0 ? row0 : row1) + bx * B2_ROWS);
+                        } else {
+                            tma_load_2d_pair(sb, &tmB, &full[stage], kcoord, rank == 0 ? row0 : row1);
+                        }
                         if (wide_piece)
                             tma_load_2d_pair(sb + BN_HALF * BK * 2, &tmB2, &full[stage], kcoord,
                                              row0 + UMMA_N + (int)rank * B2_ROWS);
@@ -590,7 +618,7 @@ static int launch_variant(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
     // EPI_LINEAR deals the last round out in 64-column pieces: up to 4 workers per tile can be put to use
-    const long long useful = (EPI == EPI_LINEAR && geom.whole_tiles == 0) ? tiles * C::GROUPS : tiles;
+    const long long useful = (EPI == EPI_LINEAR && geom.whole_tiles != 1) ? tiles * C::GROUPS : tiles;
     if (PAIR) {
         const long long pairs = useful < sms / 2 ? useful : sms / 2;
         cfg.gridDim = dim3((unsigned)(2 * pairs));
@@ -617,6 +645,10 @@ static int g_conv_force_wide = 0;
 // (measured, profiles/r02_conv_bench.json: with K = 9 Cin >= 2880 a narrow piece costs nearly a whole tile's time --
 // the k-loop is as long and the operand feed almost the same -- so the convolution keeps its last round whole)
 static int g_conv_whole_tiles = 1;
+// the linear layers' last round: 0 = 64-column groups dealt out evenly, 1 = whole tiles, 2 = halves / quarters, one per worker
+// (measured, profiles/r02_kernel_bench_gemm.json `split_policy`: halves / quarters +6 % on to_out, +11 % on ff.net.2 at
+// M = 16384, +28 % at M = 2048 over the even dealing of 64-column groups)
+static int g_linear_split_mode = 2;
 
 static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
                        const void* residual, void* out, long long M, int N, int K, long long lda,
@@ -695,13 +727,22 @@ static int launch_gemm(int epi, const void* x, const void* w, const void* bias,
     auto bp = static_cast<const __nv_bfloat16*>(bias);
     auto rp = static_cast<const __nv_bfloat16*>(residual);
     auto op = static_cast<__nv_bfloat16*>(out);
-    const ConvGeom none = {};
+    ConvGeom none = {};
+    none.whole_tiles = g_linear_split_mode;
+    CUtensorMap tmB2 = tmB;
+    if (epi == EPI_LINEAR) {
+        const uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
+        const uint64_t strides[1] = {(uint64_t)ldw * 2};
+        const uint32_t box[2] = {BK, B2_ROWS};
+        int rc = make_tmap_bf16(&tmB2, w, 2, dims, strides, box);
+        if (rc != kOk) return rc;
+    }
     if (epi == EPI_GEGLU) {
         return pair ? launch_variant<EPI_GEGLU, true>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles2, stream)
                     : launch_variant<EPI_GEGLU, false>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles1, stream);
     }
-    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles2, stream)
-                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmB, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles1, stream);
+    return pair ? launch_variant<EPI_LINEAR, true>(tmA, tmB, tmB2, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles2, stream)
+                : launch_variant<EPI_LINEAR, false>(tmA, tmB, tmB2, tmO, tmR, bp, rp, op, (int)M, N, K, (int)ldo, (int)ldr, none, tiles1, stream);
 }
 
 // Convolution over channels-last images as an implicit GEMM (see the CONV notes at the top): taps_h x taps_w filter
@@ -869,8 +910,12 @@ extern "C" int cgs_gemm_set_variant(int variant) {
         cgs::g_conv_force_wide = variant - 10;
         return cgs::kOk;
     }
-    if (variant == 20 || variant == 21) {      // 20: the convolution's last round of tiles stays whole (default), 21: pieces
-        cgs::g_conv_whole_tiles = 21 - variant;
+    if (variant >= 20 && variant <= 22) {      // the convolution's last round: 20 whole tiles (default), 21 64-column
+        cgs::g_conv_whole_tiles = variant == 20 ? 1 : variant == 21 ? 0 : 2;      // groups, 22 halves / quarters
+        return cgs::kOk;
+    }
+    if (variant >= 30 && variant <= 32) {      // the linear layers' last round: 30 64-column groups, 31 whole, 32 halves / quarters
+        cgs::g_linear_split_mode = variant - 30;
         return cgs::kOk;
     }
     if (variant < 0 || variant > 2) {

@@ -152,6 +152,38 @@ def bench_conv():
     return out
 
 
+def bench_split():
+    """How the last, partly filled round of tiles is scheduled (cgs_gemm_set_variant 30-32 linear, 20-22 convolution):
+    64-column groups dealt out evenly / whole tiles / halves or quarters with at most one piece per worker."""
+    out = []
+    lib = N.load_library()
+    cl = torch.channels_last
+    for label, M, K, Nn in [("L2_to_out", 16384, 1280, 1280), ("L2_ff_out", 16384, 5120, 1280), ("L1_to_out", 65536, 640, 640),
+                            ("L1_ff_out", 65536, 2560, 640), ("L2_qkv", 16384, 1280, 3840), ("b4_L2_ff_out", 8192, 5120, 1280),
+                            ("b1_L2_ff_out", 2048, 5120, 1280)]:
+        x, w, b, r = rnd((M, K)), rnd((Nn, K), scale=K ** -0.5), rnd((Nn,), scale=0.1), rnd((M, Nn))
+        flops = 2.0 * M * K * Nn
+        row = {"kernel": "split_policy", "case": label, "M": M, "K": K, "N": Nn}
+        for v, name in ((30, "groups64"), (31, "whole"), (32, "halves_quarters")):
+            lib.cgs_gemm_set_variant(v)
+            row[name + "_tflops"] = round(flops / timeit(lambda: N.linear(x, w, b, r), iters=30) / 1e9, 1)
+        lib.cgs_gemm_set_variant(30)
+        out.append(row)
+    for label, n, hw, cin, cout in [("conv_L2_1280_1280", 16, 32, 1280, 1280), ("conv_L2_2560_1280", 16, 32, 2560, 1280),
+                                    ("conv_b1_L2_1280_1280", 2, 32, 1280, 1280), ("conv_b1_L2_2560_1280", 2, 32, 2560, 1280)]:
+        x = rnd((n, cin, hw, hw)).contiguous(memory_format=cl)
+        w = rnd((cout, cin, 3, 3), scale=(9 * cin) ** -0.5).contiguous(memory_format=cl)
+        b = rnd((cout,), scale=0.1)
+        flops = 2.0 * n * hw * hw * 9 * cin * cout
+        row = {"kernel": "split_policy", "case": label}
+        for v, name in ((21, "groups64"), (20, "whole"), (22, "halves_quarters")):
+            lib.cgs_gemm_set_variant(v)
+            row[name + "_tflops"] = round(flops / timeit(lambda: N.conv3x3(x, w, b), iters=30) / 1e9, 1)
+        lib.cgs_gemm_set_variant(20)
+        out.append(row)
+    return out
+
+
 def bench_geglu():
     out = []
     for label, M, K, Nn in [("sdxl1024_L2", 16 * 1024, 1280, 5120), ("sdxl1024_L1", 16 * 4096, 640, 2560),
@@ -225,7 +257,7 @@ def bench_tail():
 
 def main():
     which = sys.argv[1:] or ["attn", "geglu", "linear", "ln", "tail"]
-    fns = {"conv": bench_conv, "gemmv": bench_gemm_variants, "attn": bench_attn, "geglu": bench_geglu, "linear": bench_linear, "ln": bench_ln, "tail": bench_tail}
+    fns = {"split": bench_split, "conv": bench_conv, "gemmv": bench_gemm_variants, "attn": bench_attn, "geglu": bench_geglu, "linear": bench_linear, "ln": bench_ln, "tail": bench_tail}
     results = []
     for w in which:
         for r in fns[w]():
