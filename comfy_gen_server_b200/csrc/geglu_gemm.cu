@@ -35,13 +35,16 @@
 // the gate rows.)
 //
 // Wave quantisation (EPI_LINEAR): the SDXL linears (M = 16384 / 65536, N = 1280 / 640) give 4.3 rounds of tiles, and
-// one image per GPU gives 80 tiles for 148 SMs. The tiles of the last, partly filled round are therefore dealt out
-// in 64-column pieces to ALL workers: a worker's piece is a narrower MMA (N = 64 .. 256) on the same A rows, an
-// independent set of output columns -- no reduction, no workspace, and every output element is still the same sum in
-// the same order, so results do not change. (Splitting those tiles along K instead -- partial accumulators through
-// global memory -- was built and measured first: 19 MB of fp32 partials per launch cost as much as the idle SMs.)
+// one image per GPU gives 80 tiles for 148 SMs. The tiles of the last, partly filled round are therefore cut along N
+// into halves or quarters (a narrower MMA on the same A rows: an independent set of output columns -- no reduction,
+// no workspace, and every output element is still the same sum in the same order, so results do not change), but
+// only as far as every worker still gets at most ONE piece: a piece is not proportionally cheaper than a tile (same
+// A traffic, same k-loop, lower arithmetic intensity), so a worker with two of them would be the slowest of the
+// round. On CTA pairs a narrow piece stages just the B rows it needs (32-row boxes). Measured against the first
+// scheme of this round (64-column groups dealt out evenly, some workers with two): +6 % on to_out, +11 % on
+// ff.net.2, +28 % at M = 2048. (Splitting those tiles along K instead -- partial accumulators through global
+// memory -- was built and measured first: 19 MB of fp32 partials per launch cost as much as the idle SMs.)
 // The same mechanism serves the last column of tiles when N is not a multiple of 256 (N = 640: an N = 128 MMA).
-//
 //
 // CONV (EPI_LINEAR, CTA pairs): the same GEMM as a 3x3 / stride 1 / pad 1 convolution over a channels-last image
 // (reference: ResBlock / Upsample convolutions, comfy/ldm/modules/diffusionmodules/openaimodel.py:83-96, 177-232;
