@@ -39,6 +39,7 @@ _SIGNATURES = {
     "cgs_gemm_set_variant": [_c_int],
     "cgs_conv3x3_nhwc_fwd": [_c_void_p] * 5 + [_c_int] * 5 + [_c_ll] * 3 + [_c_void_p],
     "cgs_upsample2x_conv3x3_nhwc_fwd": [_c_void_p] * 4 + [_c_int] * 5 + [_c_ll] * 2 + [_c_void_p],
+    "cgs_softmax_rows_fwd": [_c_void_p, _c_ll, _c_int, _c_ll, _c_float, _c_void_p],
     "cgs_unet_input_fwd": [_c_void_p] * 3 + [_c_ll, _c_ll, _c_int, _c_float, _c_void_p],
     "cgs_cfg_denoise_fwd": [_c_void_p] * 3 + [_c_int, _c_void_p, _c_float, _c_int, _c_float, _c_void_p,
                                               _c_ll, _c_ll, _c_void_p],
@@ -483,6 +484,17 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
                                            _stream(x))
     _check(rc, "cgs_linear_fwd")
     return out
+
+
+def softmax_rows_(x: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+    """x <- softmax(scale * x, dim=-1) in place; x [rows, cols] bf16 with contiguous rows."""
+    _require_cuda("softmax_rows x", x, torch.bfloat16)
+    if x.dim() != 2 or x.stride(1) != 1:
+        raise RuntimeError("softmax_rows: expected a 2-D tensor with contiguous rows")
+    with _Launch("softmax_rows", x, 4.0 * x.numel()):
+        rc = load_library().cgs_softmax_rows_fwd(x.data_ptr(), x.shape[0], x.shape[1], x.stride(0), float(scale), _stream(x))
+    _check(rc, "cgs_softmax_rows_fwd")
+    return x
 
 
 def conv3x3_tile_efficiency(h: int, w: int) -> float:

@@ -16,7 +16,8 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libcgs_b200.so")
 STAMP_PATH = os.path.join(PKG_DIR, ".libcgs_b200.stamp")
 
-SOURCES = ["common.cu", "layernorm.cu", "sampler_tail.cu", "geglu_gemm.cu", "attention.cu", "groupnorm.cu", "transpose.cu"]
+SOURCES = ["common.cu", "layernorm.cu", "sampler_tail.cu", "geglu_gemm.cu", "attention.cu", "groupnorm.cu", "transpose.cu",
+           "softmax.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -305,6 +305,16 @@ int cgs_upsample2x_conv3x3_nhwc_fwd(const void* x, const void* w4, const void* b
                                     int W, int Cin, int Cout, long long ldx, long long ldy, void* stream);
 
 /*
+ * Row softmax in place: x[r, 0:cols] <- softmax(scale * x[r, 0:cols]), bf16 storage, fp32 arithmetic. The normalisation
+ * step of the VAE decoder's mid-block attention (AttnBlock, one head of d = 512), which runs the reference's
+ *   s1 = torch.bmm(q, k) * scale;  s2 = torch.nn.functional.softmax(s1, dim=2);  r1 = torch.bmm(v, s2.permute(0, 2, 1))
+ * (comfy/ldm/modules/diffusionmodules/model.py:160-196 slice_attention / normal_attention, in the compute dtype) with the
+ * two matrix products on cgs_linear_fwd.
+ *   x [rows, cols] bf16, `ld` elements between rows; cols a multiple of 8, at most 32768; scale > 0.
+ */
+int cgs_softmax_rows_fwd(void* x, long long rows, int cols, long long ld, float scale, void* stream);
+
+/*
  * The same tail for a cond / uncond pair that is split across two GPUs (multi-GPU placement):
  * the exchange of the two halves of the model output and cfg_function + sampler update (comfy/samplers.py:234-247,
  * comfy/k_diffusion/sampling.py:137-143, 583-592) in ONE launch, instead of a collective followed by the tail.

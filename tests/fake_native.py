@@ -110,6 +110,12 @@ def upsample2x_conv3x3(x, w4, bias=None):
     return F.conv2d(F.interpolate(x, scale_factor=2, mode="nearest"), w4, bias, padding=1)
 
 
+def softmax_rows_(x, scale=1.0):
+    _count("softmax_rows")
+    x.copy_(torch.softmax(x.float() * scale, dim=-1))
+    return x
+
+
 def unet_input(x, sigma, copies, sigma_data=1.0):
     _count("unet_input")
     s = sigma.view(-1, *([1] * (x.dim() - 1)))
@@ -162,7 +168,7 @@ def patched():
     """Swap the stand-ins into _native and point layers.py at (cpu, fp32)."""
     from comfy_gen_server_b200 import _native, layers
     names = ["attention", "layer_norm", "add_layer_norm_", "group_norm", "residual_add", "cat_channels",
-             "upsample_nearest2x", "transpose_add", "geglu", "linear", "conv3x3", "upsample2x_conv_weights", "upsample2x_conv3x3", "unet_input", "cfg_denoise",
+             "upsample_nearest2x", "transpose_add", "geglu", "linear", "conv3x3", "upsample2x_conv_weights", "upsample2x_conv3x3", "softmax_rows_", "unet_input", "cfg_denoise",
              "sampler_step_euler", "sampler_step_dpmpp2m", "cfg_sampler_tail"]
     saved = {n: getattr(_native, n) for n in names}
     saved_layers = (layers.ACT_DTYPE, layers.DEVICE_TYPE)

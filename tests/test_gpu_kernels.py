@@ -419,6 +419,24 @@ def test_linear_vs_oracle(M, K, Nn, res):
     assert (y - ref).abs().max() <= ulp_tol(ref)
 
 
+# ------------------------------------------------------------------------------------------ row softmax
+@pytest.mark.parametrize("rows,cols,scale", [(7, 8, 1.0), (300, 1024, 512 ** -0.5), (64, 16384, 0.044), (3, 32768, 0.1),
+                                             (5, 4104, 2.0)])
+def test_softmax_rows_vs_torch(rows, cols, scale):
+    """cgs_softmax_rows_fwd against torch.softmax in fp32 (the reference's slice_attention, model.py:175-180)."""
+    x = bf(randn((rows, cols), 1, 6.0))
+    ref = torch.softmax(x.float().cpu() * scale, dim=-1)
+    y = N().softmax_rows_(x.clone(), scale).float().cpu()
+    assert (y - ref).abs().max() <= float(ref.max()) * 2 ** -7 + 1e-6
+    assert ((y.sum(-1) - 1).abs() < 2e-2).all()
+    # a strided view (rows of a wider matrix)
+    wide = bf(randn((rows, cols + 64), 2, 3.0))
+    keep = wide[:, cols:].clone()
+    N().softmax_rows_(wide[:, :cols], scale)
+    assert torch.equal(wide[:, cols:], keep)
+    assert (wide[:, :cols].float().sum(-1) - 1).abs().max() < 2e-2
+
+
 # ------------------------------------------------------------------------------------------ 3x3 convolution
 CONV_SHAPES = [
     # n, H, W, Cin, Cout, bias, residual

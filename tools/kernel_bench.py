@@ -60,7 +60,13 @@ def bench_attn():
     cases = [("sdxl1024_L1_self", 16, 10, 4096, 4096, 64), ("sdxl1024_L2_self", 16, 20, 1024, 1024, 64),
              ("sdxl2048_L1_self", 2, 10, 16384, 16384, 64), ("sdxl1024_L1_cross77", 16, 10, 4096, 77, 64),
              ("sdxl1024_L2_cross77", 16, 20, 1024, 77, 64), ("sd15_L0_self_d40", 32, 8, 4096, 4096, 40),
-             ("sd15_L1_self_d80", 32, 8, 1024, 1024, 80), ("sd21_L0_self", 16, 5, 9216, 9216, 64)]
+             ("sd15_L1_self_d80", 32, 8, 1024, 1024, 80), ("sd21_L0_self", 16, 5, 9216, 9216, 64),
+             # one / two images per GPU (strong scaling on 8 / 4 GPUs)
+             ("b1_sdxl_L2_self", 2, 20, 1024, 1024, 64), ("b1_sdxl_L1_self", 2, 10, 4096, 4096, 64),
+             ("b2_sdxl_L2_self", 4, 20, 1024, 1024, 64), ("b2_sdxl_L1_self", 4, 10, 4096, 4096, 64)]
+    only = os.environ.get("ATTN_CASES")
+    if only:
+        cases = [c for c in cases if any(c[0].startswith(o) for o in only.split(","))]
     for label, B, H, Nq, Nk, d in cases:
         q, k, v = rnd((B, Nq, H * d)), rnd((B, Nk, H * d)), rnd((B, Nk, H * d))
         ms = timeit(lambda: N.attention(q, k, v, H))
