@@ -26,12 +26,7 @@ from . import layers
 from .layers import ORIGINAL, on_fast_device, linear_plain, groupnorm_apply
 
 
-def _ver(t) -> int:
-    """Version counter of a tensor; inference tensors do not track one (treated as immutable)."""
-    try:
-        return t._version
-    except RuntimeError:
-        return -1
+_ver = layers.tensor_version
 
 
 # ----------------------------------------------------------------------------------------------

@@ -132,6 +132,15 @@ def conv_nobias(conv, x):
     return conv._conv_forward(x, conv.weight, None)
 
 
+def tensor_version(t) -> int:
+    """Version counter of a tensor; inference tensors do not track one (treated as immutable: the reference's
+    executor loads checkpoints under torch.inference_mode(), execution.py:537)."""
+    try:
+        return t._version
+    except RuntimeError:
+        return -1
+
+
 def conv3x3_native_ok(conv, x) -> bool:
     """The convolution can run on the library's implicit GEMM (cgs_conv3x3_nhwc_fwd): 3x3, stride 1, padding 1,
     channels-last bf16 input and weight, and an image whose pixel tiles are mostly real pixels."""
@@ -171,7 +180,7 @@ def upsample2x_conv3x3(conv, x, bias=None):
     The pre-summed phase weights are derived once per weight tensor and kept on the module."""
     if not (_native.FEATURES["native_upconv"] and conv3x3_native_ok(conv, x)):
         return None
-    key = (conv.weight.data_ptr(), conv.weight._version)
+    key = (conv.weight.data_ptr(), tensor_version(conv.weight))
     cached = conv.__dict__.get("_cgs_upconv")
     if cached is None or cached[0] != key:
         cached = (key, _native.upsample2x_conv_weights(conv.weight))

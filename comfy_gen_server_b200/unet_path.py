@@ -121,7 +121,8 @@ def _ensure_channels_last_weights(unet) -> None:
     patch replaced since): cuDNN then needs no per-call weight transform."""
     for p in unet.parameters():
         if p.dim() == 4 and not p.is_contiguous(memory_format=torch.channels_last):
-            with torch.inference_mode(False):        # the parameter must stay usable outside inference mode
+            with torch.inference_mode(p.is_inference()):    # an inference tensor stays one (the server loads checkpoints
+                # under torch.inference_mode()), a normal tensor stays usable outside inference mode
                 p.data = p.data.contiguous(memory_format=torch.channels_last)
 
 

@@ -34,7 +34,8 @@ def _channels_last(module, x):
     """x and the module's convolution weights in channels-last (weights converted in place, once)."""
     for p in module.parameters(recurse=True):
         if p.dim() == 4 and not p.is_contiguous(memory_format=_CL):
-            with torch.inference_mode(False):        # the parameter must stay usable outside inference mode
+            with torch.inference_mode(p.is_inference()):    # an inference tensor stays one (the server loads checkpoints
+                # under torch.inference_mode()), a normal tensor stays usable outside inference mode
                 p.data = p.data.contiguous(memory_format=_CL)
     return x.contiguous(memory_format=_CL)
 
@@ -74,8 +75,8 @@ MAX_SCORE_TOKENS = 32768          # the [tokens, tokens] score matrix of one ima
 
 def _qkv_weight(self):
     """The three 1x1 convolutions q, k, v as one [3C, C] GEMM weight (+ bias), derived once per set of weights."""
-    key = tuple((m.weight.data_ptr(), m.weight._version, m.bias.data_ptr(), m.bias._version)
-                for m in (self.q, self.k, self.v))
+    ver = layers.tensor_version
+    key = tuple((m.weight.data_ptr(), ver(m.weight), m.bias.data_ptr(), ver(m.bias)) for m in (self.q, self.k, self.v))
     cached = self.__dict__.get("_cgs_vae_qkv")
     if cached is None or cached[0] != key:
         c = self.in_channels

@@ -357,3 +357,23 @@ def test_upsample_conv_phase_weights_are_the_same_convolution():
             xp = F.pad(x, (1 - b, b, 1 - a, a))
             out[:, :, a::2, b::2] = F.conv2d(xp, k)
     assert (out - ref).abs().max() < 1e-5          # (the weights are summed in fp32)
+
+
+@pytest.mark.parametrize("created_in_inference", [False, True])
+@pytest.mark.parametrize("converted_in_inference", [False, True])
+@pytest.mark.parametrize("used_in_inference", [False, True])
+def test_channels_last_weight_conversion_keeps_parameters_usable(created_in_inference, converted_in_inference,
+                                                                 used_in_inference):
+    """The in-place channels-last conversion of convolution weights must leave a parameter as it found it: the
+    reference's executor loads checkpoints and samples under torch.inference_mode() (execution.py:537), tests and
+    scripts do not."""
+    from comfy_gen_server_b200 import unet_path, vae_path
+    for convert in (unet_path._ensure_channels_last_weights, lambda m: vae_path._channels_last(m, torch.zeros(1, 8, 4, 4))):
+        with torch.inference_mode(created_in_inference):
+            conv = torch.nn.Conv2d(8, 8, 3, padding=1)
+        with torch.inference_mode(converted_in_inference):
+            convert(conv)
+        assert conv.weight.is_contiguous(memory_format=torch.channels_last)
+        assert conv.weight.is_inference() == created_in_inference
+        with torch.inference_mode(used_in_inference), torch.no_grad():
+            assert conv(torch.randn(1, 8, 4, 4)).shape == (1, 8, 4, 4)

@@ -470,3 +470,55 @@ def test_vae_decode_with_install_vs_reference_golden():
     t_ref, o2 = _reference_itself(lambda: timed(dec_ref))
     print(f"VAE decode 1024^2: {t_ours * 1e3:.1f} ms with install(), {t_ref * 1e3:.1f} ms the reference itself")
     assert cosine(o1.float().cpu(), o2.float().cpu()) > 0.999
+
+
+def test_vae_encode_with_install_vs_reference_itself():
+    """The VAE encoder (img2img / in-painting: comfy/ldm/modules/diffusionmodules/model.py Encoder) shares ResnetBlock
+    and AttnBlock with the decoder, so install() moves it onto the kernels too: bf16 with install() against the
+    reference's own fp32 forward of the same seeded weights (no fixture: the staged reference runs here), with the
+    unmodified reference in bf16 as the yardstick."""
+    import copy
+    import comfy.ldm.modules.diffusionmodules.model as vm
+    from comfy_gen_server_b200 import _native
+    ddconfig = {'double_z': True, 'z_channels': 4, 'resolution': 256, 'in_channels': 3, 'out_ch': 3, 'ch': 128,
+                'ch_mult': [1, 2, 4, 4], 'num_res_blocks': 2, 'attn_resolutions': [], 'dropout': 0.0}
+    enc = vm.Encoder(**ddconfig)
+    shapes = {k: tuple(v.shape) for k, v in enc.state_dict().items()}
+    enc.load_state_dict(uc.seeded_state_dict(shapes, 11, residual_damp=1.0))
+    enc = enc.to(DEV).eval()
+    img = randn((1, 3, 256, 256), 7).to(DEV).clamp(-1, 1)
+    with torch.inference_mode():
+        ref = _reference_itself(lambda: enc(img).float().cpu())                    # fp32, the reference's own code
+        enc_bf = copy.deepcopy(enc).to(torch.bfloat16)
+        enc_ref_bf = copy.deepcopy(enc_bf)
+        _native.reset_launch_counters()
+        out = enc_bf(img.bfloat16()).float().cpu()
+        launched = dict(_native.LAUNCHES)
+        base = _reference_itself(lambda: enc_ref_bf(img.bfloat16()).float().cpu())
+    assert launched.get("conv3x3", 0) >= 20 and launched.get("groupnorm_nhwc", 0) >= 20, launched
+    c, cb = cosine(out, ref), cosine(base, ref)
+    print(f"VAE encode 256^2: cosine vs the reference's fp32 forward {c:.6f} (the reference itself in bf16: {cb:.6f})")
+    assert c >= 0.999 and c >= cb - 2e-4
+
+
+def test_model_loaded_under_inference_mode_samples_the_same():
+    """The reference's executor runs every node -- checkpoint loading included -- under torch.inference_mode()
+    (execution.py:537), so in the server the weights are inference tensors: no version counters, and the in-place
+    channels-last conversion has to keep them that way. Same latents as with ordinary tensors."""
+    import comfy.sample
+    from comfy_gen_server_b200 import models
+    g = load_golden("e2e_sd15_config1")
+    seed = int(g["seed"])
+    latent = torch.zeros(1, 4, 64, 64)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    args = (noise, 3, 7.0, "euler", "normal", [[g["positive"], {}]], [[g["negative"], {}]], latent)
+    patcher, _ = models.build_model("sd15", DEV, seed=seed)
+    want = _sample(patcher, *args, seed=seed)
+    del patcher
+    torch.cuda.empty_cache()
+    with torch.inference_mode():
+        patcher, model = models.build_model("sd15", DEV, seed=seed)
+        assert model.diffusion_model.input_blocks[1][0].in_layers[2].weight.is_inference()
+        got = comfy.sample.sample(patcher, *args, seed=seed, disable_pbar=True)
+        got2 = comfy.sample.sample(patcher, *args, seed=seed, disable_pbar=True)
+    assert torch.equal(got, want) and torch.equal(got2, want)
