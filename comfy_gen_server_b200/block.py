@@ -115,6 +115,15 @@ def cross_attention_cached(attn, x, context):
     return ref.optimized_attention(attn.to_q(x), kv[1], kv[2], attn.heads)
 
 
+def derived_state(module: torch.nn.Module) -> list:
+    """Every derived object this package keeps on the sub-modules of `module` (fused QKV weights, cached K / V,
+    pre-summed convolution weights). A captured step graph holds on to this list: the graph has the tensors' addresses
+    baked in, while the modules replace them whenever the weights they were derived from move (an unload / reload
+    through a LoRA clone frees them) -- and a later reload can put every parameter back at the address the graph's
+    key remembers."""
+    return [v for m in module.modules() for k, v in m.__dict__.items() if k.startswith("_cgs_")]
+
+
 def release_caches(module: torch.nn.Module) -> None:
     """Drop every derived tensor this package attached to the modules of `module` (fused QKV weights, K/V caches)."""
     for m in module.modules():

@@ -278,6 +278,7 @@ class FusedDenoise:
         for k, v in g["counts"].items():
             _native.LAUNCHES[k] -= v
         g["graph"] = graph
+        g["derived"] = B.derived_state(self.model.diffusion_model)      # what the capture baked in stays alive with it
         cache = self.model.__dict__.setdefault("_cgs_step_graphs", collections.OrderedDict())
         cache[self._graph_key(x)] = g
         while len(cache) > 2:                              # a graph pins its activation pool: keep the two latest

@@ -522,3 +522,44 @@ def test_model_loaded_under_inference_mode_samples_the_same():
         got = comfy.sample.sample(patcher, *args, seed=seed, disable_pbar=True)
         got2 = comfy.sample.sample(patcher, *args, seed=seed, disable_pbar=True)
     assert torch.equal(got, want) and torch.equal(got2, want)
+
+
+def test_lora_patches_through_the_model_patcher():
+    """The reference's LoRA path (ModelPatcher.add_patches -> patch_model -> calculate_weight, model_patcher.py:198-208,
+    283-360) replaces weight tensors under the caches this package keeps on the modules (fused QKV weights, cached
+    text K / V, pre-summed up-sampling convolution weights, captured step graphs): a patched clone must sample what
+    the unmodified reference samples with the same patches, and the unpatched model afterwards exactly what it
+    sampled before."""
+    import comfy.sample
+    from comfy_gen_server_b200 import models
+    g = load_golden("e2e_sd15_config1")
+    seed = int(g["seed"])
+    latent = torch.zeros(1, 4, 64, 64)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    args = (noise, 3, 7.0, "euler", "normal", [[g["positive"], {}]], [[g["negative"], {}]], latent)
+    patcher, model = models.build_model("sd15", DEV, seed=seed)
+    base = _sample(patcher, *args, seed=seed)
+    c0 = cosine(base, _reference_itself(lambda: _sample(patcher, *args, seed=seed)))     # bf16 against bf16, no patches
+
+    sd = model.state_dict()
+    wanted = ("attn1.to_q.weight", "attn1.to_k.weight", "attn1.to_v.weight", "attn1.to_out.0.weight", "attn2.to_k.weight",
+              "ff.net.0.proj.weight", "ff.net.2.weight", "0.in_layers.2.weight", "0.out_layers.3.weight", "1.conv.weight")
+    keys = [next(k for k in sd if k.endswith(w)) for w in wanted]
+    gen = torch.Generator().manual_seed(5)
+    patches = {}
+    for k in keys:
+        w = sd[k]
+        up = torch.randn(w.shape[0], 4, generator=gen) * 0.05
+        down = torch.randn(4, w[0].numel(), generator=gen) * 0.05
+        patches[k] = ("lora", (up, down, 4.0, None, None))
+    lora = patcher.clone()
+    assert sorted(lora.add_patches(patches, 1.0)) == sorted(keys)
+    got = _sample(lora, *args, seed=seed)
+    ref = _reference_itself(lambda: _sample(lora, *args, seed=seed))
+    c = cosine(got, ref)
+    print(f"LoRA-patched SD1.5, 3 steps: cosine vs the unmodified reference with the same patches {c:.6f}; "
+          f"vs the unpatched run {cosine(got, base):.6f}")
+    print(f"(unpatched: this path vs the unmodified reference, both bf16: {c0:.6f})")
+    assert c > 0.999 and c > c0 - 3e-4 and cosine(got, base) < 0.9999
+    again = _sample(patcher, *args, seed=seed)
+    assert torch.equal(again, base)
