@@ -563,3 +563,26 @@ def test_lora_patches_through_the_model_patcher():
     assert c > 0.999 and c > c0 - 3e-4 and cosine(got, base) < 0.9999
     again = _sample(patcher, *args, seed=seed)
     assert torch.equal(again, base)
+
+
+def test_step_graph_cache_eviction_and_recapture():
+    """A model keeps the two most recent captured steps; a third shape evicts the oldest, whose next use captures
+    again. Every replayed run equals the launch-by-launch run of the same inputs."""
+    import comfy.sample
+    g = load_golden("e2e_tiny_sd15_euler")
+    seed = int(g["seed"])
+    patcher = _model("tiny_sd15", seed)
+    pos, neg = _prompts(g)
+
+    def run(batch, graph):
+        p = patcher.clone()
+        p.model_options["cuda_graph"] = graph
+        latent = torch.zeros(batch, 4, 16, 16)
+        noise = comfy.sample.prepare_noise(latent, seed + batch)
+        rep = lambda c: [[c[0][0].repeat(batch // 2 if batch > 1 else 1, 1, 1)[:batch], c[0][1]]]
+        return _sample(p, noise, 4, 7.0, "euler", "normal", rep(pos), rep(neg), latent, seed=seed)
+    eager = {b: run(b, False) for b in (1, 2, 4)}
+    for b in (1, 2, 4, 1, 4, 2):
+        assert torch.equal(run(b, True), eager[b]), b
+    cache = patcher.model.__dict__.get("_cgs_step_graphs")
+    assert cache is not None and len(cache) <= 2
