@@ -359,6 +359,7 @@ def run_ours(args):
             geglu_ms, geglu_flops, geglu_n = family_pass("geglu_gemm", geglu_steps)
         attn_steps = min(args.steps, 6)
         attn_ms, attn_flops, attn_n = family_pass("attention", attn_steps)
+        xattn_ms, xattn_bytes, xattn_n = family_pass("attention_cross", min(args.steps, 3))
         ln_ms, ln_bytes, ln_n = family_pass("add_layernorm", min(args.steps, 3))
         pln_ms, pln_bytes, pln_n = family_pass("layernorm", min(args.steps, 3))
         lin_ms, lin_flops, lin_n = family_pass("linear", min(args.steps, 3))
@@ -433,10 +434,17 @@ def run_ours(args):
                          "launches_timed": geglu_n, "ms_in_kernel_per_step": geglu_ms / geglu_steps,
                          "timed": "inside the timed region" if time_in_region else "separate launch-by-launch pass",
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['source']})"},
-            "roofline_attention": {"kernel": "attn_fwd_kernel (cgs_attention_fwd, self + cross)", "bound": "tensor",
+            "roofline_attention": {"kernel": "attn_fwd_kernel (cgs_attention_fwd, self-attention: 4096 / 1024 tokens, d = 64)", "bound": "tensor",
                                    "achieved": atf, "peak": peak_tf, "unit": "TFLOP/s",
                                    "frac": atf / peak_tf if peak_tf else None, "launches_timed": attn_n,
                                    "ms_in_kernel_per_step": attn_ms / attn_steps},
+            "roofline_attention_cross": {"kernel": "attn_fwd_kernel<.., 96> (cgs_attention_fwd, text cross-attention: 77 keys)",
+                                         "bound": "hbm",
+                                         "achieved": xattn_bytes / (xattn_ms * 1e-3) / 1e9 if xattn_ms > 0 else 0.0,
+                                         "peak": peaks["hbm_gbs"], "unit": "GB/s", "launches_timed": xattn_n,
+                                         "frac": (xattn_bytes / (xattn_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if xattn_ms > 0 else 0.0,
+                                         "ms_in_kernel_per_step": xattn_ms / min(args.steps, 3),
+                                         "note": "algorithmic bytes = Q + O + K + V once"},
             "roofline_add_layernorm": {"kernel": "layernorm_kernel<ADD> (cgs_add_layernorm_fwd)", "bound": "hbm",
                                        "achieved": lnbw, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                        "frac": lnbw / peaks["hbm_gbs"], "launches_timed": ln_n,

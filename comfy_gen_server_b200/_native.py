@@ -218,7 +218,10 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
                 _stream(q))
         _check(rc, "cgs_attention_masked_fwd")
         return out
-    with _Launch("attention", q, 4.0 * B * heads * Nq * Nk * d):
+    # text cross-attention (77 / 154 keys) moves Q and O once for a handful of FLOPs: HBM-bound, accounted in bytes
+    cross = Nk <= 192 and Nq > Nk
+    work = 2.0 * (2 * B * Nq * inner + 2 * B * Nk * inner) if cross else 4.0 * B * heads * Nq * Nk * d
+    with _Launch("attention_cross" if cross else "attention", q, work):
         rc = load_library().cgs_attention_fwd(
             q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, heads, Nq, Nk, d,
             q.stride(0), q.stride(1), d, k.stride(0), k.stride(1), d, v.stride(0), v.stride(1), d,
