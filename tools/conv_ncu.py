@@ -5,6 +5,8 @@ sys.path.insert(0, ROOT)
 from comfy_gen_server_b200 import _native as N
 if os.environ.get("CGS_LIB"):          # a private variant build (tools/gemm_dbg.sh)
     N._lib = N.load_library(os.path.join(ROOT, os.environ["CGS_LIB"]))
+if os.environ.get("CONV_VARIANT"):      # cgs_gemm_set_variant code (11 tiles of 256, 12 of 320, 13 of 192 columns)
+    assert N.load_library().cgs_gemm_set_variant(int(os.environ["CONV_VARIANT"])) == 0
 cl = torch.channels_last
 cases = [(16, 128, 320, 320), (16, 128, 960, 320), (16, 64, 640, 640), (16, 64, 1920, 640), (16, 32, 1280, 1280)]
 for n, hw, cin, cout in cases:
