@@ -461,7 +461,7 @@ extern "C" int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const v
 // What the caller has to know:
 //   * the first call on each device looks up the array's device address (cudaGetSymbolAddress) with that device
 //     current -- make that first call during set-up, before any stream capture is started;
-//   * problems whose partial statistics do not fit (N * chunks * groups * 8 bytes > 1 MiB; roughly N > 32 at the
+//   * problems whose partial statistics do not fit (N * (chunks + 1) * groups * 8 bytes > 1 MiB; roughly N > 32 at the
 //     largest feature maps) are refused with CGS_SCRATCH_TOO_SMALL, nothing is launched;
 //   * all calls on a device share the one array and it keeps whatever the previous call left in it. Nothing has to
 //     be zeroed between calls (the statistics kernel overwrites every slot the normalise kernel reads), but two calls

@@ -104,10 +104,11 @@ int cgs_groupnorm_fwd(const void* x, const void* add_nc, const void* gamma, cons
 
 /*
  * The same GroupNorm (+ SiLU, + addend) for channels-last activations: x, y [N, H*W, C] bf16 (torch
- * memory_format=channels_last). Two launches (partial statistics per pixel-row chunk, then normalise) that
+ * memory_format=channels_last). Two launches (partial statistics per pixel-row chunk, then normalise; three for
+ * images of 64 MB and more per sample, whose up to 1024 partials a small kernel adds up in between) that
  * communicate through `scratch`, a caller-provided device buffer of at least
  * cgs_groupnorm_nhwc_scratch_bytes(N, C, HW, groups) bytes; it need not be initialised and may be reused by the next
- * call on the same stream. C % 8 == 0, C / groups >= 8, groups <= 32, C <= 2560.
+ * call on the same stream. C % 8 == 0, C / groups >= 8 or == 4 (the VAE's 128-channel level), groups <= 32, C <= 2560.
  */
 long long cgs_groupnorm_nhwc_scratch_bytes(int N, int C, int HW, int groups);
 int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma, const void* beta, void* y,
@@ -122,7 +123,7 @@ int cgs_groupnorm_nhwc_fwd(const void* x, const void* add_nc, const void* gamma,
  * device-wide synchronisation. The partial-statistics buffer is a fixed 1 MiB array inside the library, present on
  * every GPU that loads it, for the life of the process.
  *   - Same arguments and results as cgs_groupnorm_nhwc_fwd, minus the scratch pair.
- *   - Limit: N * chunks * groups * 8 bytes (= cgs_groupnorm_nhwc_scratch_bytes) must be <= 1 MiB, else
+ *   - Limit: N * (chunks + 1) * groups * 8 bytes (= cgs_groupnorm_nhwc_scratch_bytes) must be <= 1 MiB, else
  *     CGS_SCRATCH_TOO_SMALL and nothing is launched.
  *   - The first call on a device resolves the array's address on that device; make it during set-up, before any
  *     stream capture begins.
