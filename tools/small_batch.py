@@ -31,6 +31,9 @@ def main():
     from comfy_gen_server_b200 import _native, integration, models, sampling as ks, unet_config as uc
     from comfy_gen_server_b200.guider import FusedDenoise
     integration.install()
+    for f in os.environ.get("CGS_FEATURES_OFF", "").split(","):      # A/B: switch routing features off (_native.FEATURES)
+        if f:
+            _native.FEATURES[f] = False
     import comfy.sampler_helpers, comfy.samplers, comfy.utils
     comfy.utils.PROGRESS_BAR_ENABLED = False
     dev = torch.device("cuda")
