@@ -268,6 +268,13 @@ int cgs_cfg_sampler_tail_dev_fwd(const float* x, const void* out_uncond, const v
  * Tuning switch for the micro-benchmarks (no counterpart in the reference): which mainloop cgs_geglu_gemm_fwd /
  * cgs_linear_fwd use -- 0 automatic (default), 1 one CTA per M128 x N256 tile, 2 CTA pairs (cta_group::2) on
  * M256 x N256 tiles. Both compute every output element from the same products in the same order: results are identical.
+ * Further codes, all result-neutral as well:
+ *   10 / 11 / 12   convolution tiles: automatic / 256 columns / 320 columns where Cout % 320 == 0
+ *   20 / 21 / 22   the convolution's last, partly filled round of tiles: whole tiles (default) / 64-column groups dealt
+ *                  out evenly / halves or quarters, at most one per worker
+ *   30 / 31 / 32   the same for cgs_linear_fwd: 64-column groups / whole tiles / halves or quarters (default)
+ * Returns CGS_BAD_ARGUMENT for any other value. Process-wide; meant for A/B measurements (tools/kernel_bench.py,
+ * bench.py --gemm-set), not for production code.
  */
 int cgs_gemm_set_variant(int variant);
 
