@@ -586,3 +586,57 @@ def test_step_graph_cache_eviction_and_recapture():
         assert torch.equal(run(b, True), eager[b]), b
     cache = patcher.model.__dict__.get("_cgs_step_graphs")
     assert cache is not None and len(cache) <= 2
+
+
+class _StubControl:
+    """The part of the reference's ControlBase interface that the sampling path touches (controlnet.py / samplers.py:
+    pre_run, get_control, get_models, cleanup), adding a fixed residual after the middle block."""
+    def __init__(self, residual):
+        self.residual = residual
+        self.calls = 0
+
+    def pre_run(self, model, percent_to_timestep_function):
+        pass
+
+    def get_models(self):
+        return []
+
+    def inference_memory_requirements(self, dtype):
+        return 0
+
+    def cleanup(self):
+        pass
+
+    def get_control(self, x_noisy, t, cond, batched_number):
+        self.calls += 1
+        r = self.residual.to(x_noisy.device)
+        return {"middle": [r.expand(x_noisy.shape[0], -1, -1, -1)]}
+
+
+def test_controlnet_residuals_take_the_reference_path_on_the_kernels():
+    """A cond with a control object leaves every fused level (guider, apply_model, UNetModel.forward) for the
+    reference's own code, whose blocks are still the rebound ones -- now fed NCHW activations and
+    channels-last weights left behind by an earlier fast-path run. Same latents as the unmodified reference with the
+    same control."""
+    import comfy.sample
+    from comfy_gen_server_b200 import _native, models
+    g = load_golden("e2e_sd15_config1")
+    seed = int(g["seed"])
+    latent = torch.zeros(1, 4, 64, 64)
+    noise = comfy.sample.prepare_noise(latent, seed)
+    patcher, _ = models.build_model("sd15", DEV, seed=seed)
+    plain = (noise, 3, 7.0, "euler", "normal", [[g["positive"], {}]], [[g["negative"], {}]], latent)
+    base = _sample(patcher, *plain, seed=seed)                       # fast path first: converts the conv weights
+    ctl = _StubControl(randn((1, 1280, 8, 8), 9, 0.5))
+    pos = [[g["positive"], {"control": ctl, "control_apply_to_uncond": True}]]
+    args = (noise, 3, 7.0, "euler", "normal", pos, [[g["negative"], {}]], latent)
+    _native.reset_launch_counters()
+    got = _sample(patcher, *args, seed=seed)
+    launched = dict(_native.LAUNCHES)
+    calls = ctl.calls
+    ref = _reference_itself(lambda: _sample(patcher, *args, seed=seed))
+    assert calls >= 3 and launched.get("attention", 0) > 0 and launched.get("cfg_sampler_tail", 0) == 0, (calls, launched)
+    c, cb = cosine(got, ref), cosine(got, base)
+    print(f"control residual, SD1.5, 3 steps: cosine vs the unmodified reference {c:.6f}; vs the run without control {cb:.6f}")
+    assert c > 0.999 and cb < 0.9999
+    assert torch.equal(_sample(patcher, *plain, seed=seed), base)    # and back on the fast path
