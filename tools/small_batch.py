@@ -31,6 +31,9 @@ def main():
     from comfy_gen_server_b200 import _native, integration, models, sampling as ks, unet_config as uc
     from comfy_gen_server_b200.guider import FusedDenoise
     integration.install()
+    if os.environ.get("CGS_MIN_ROWS"):                              # A/B: from how many rows on the linears run on this library
+        from comfy_gen_server_b200 import block
+        block.NATIVE_LINEAR_MIN_ROWS = int(os.environ["CGS_MIN_ROWS"])
     for f in os.environ.get("CGS_FEATURES_OFF", "").split(","):      # A/B: switch routing features off (_native.FEATURES)
         if f:
             _native.FEATURES[f] = False
