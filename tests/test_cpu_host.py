@@ -377,3 +377,74 @@ def test_channels_last_weight_conversion_keeps_parameters_usable(created_in_infe
         assert conv.weight.is_inference() == created_in_inference
         with torch.inference_mode(used_in_inference), torch.no_grad():
             assert conv(torch.randn(1, 8, 4, 4)).shape == (1, 8, 4, 4)
+
+
+def _fill(module, seed):
+    """Seeded weights for a module built with the reference's no-init operator classes."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in module.named_parameters():
+            if p.dim() == 1 and ("norm" in name or name.endswith("in_layers.0.weight") or name.endswith("out_layers.0.weight")
+                                 or name.endswith("out.0.weight")) and name.endswith("weight"):
+                p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g))
+            else:
+                p.copy_(torch.randn(p.shape, generator=g) * (0.1 if p.dim() == 1 else p[0].numel() ** -0.5))
+
+
+def test_channels_last_unet_path_on_the_cpu_equals_the_reference(reference_tree):
+    """The wide-UNet host logic that the tiny golden models never reach (model_channels / 32 >= 8): channels-last
+    pipeline, 3x3 convolutions with bias / skip image folded into them, interpolate + conv, deferred up-sampling conv
+    bias in the skip concatenation -- on fp32 CPU tensors with torch stand-ins for the kernels, against the reference's
+    own UNetModel.forward of the same module."""
+    import comfy.ops
+    import comfy.ldm.modules.diffusionmodules.openaimodel as ref_unet
+    import fake_native
+    from comfy_gen_server_b200 import integration
+    cfg = {'use_checkpoint': False, 'image_size': 32, 'out_channels': 4, 'use_spatial_transformer': True, 'legacy': False,
+           'adm_in_channels': None, 'in_channels': 4, 'model_channels': 256, 'num_res_blocks': [1, 1],
+           'transformer_depth': [1, 1], 'channel_mult': [1, 2], 'transformer_depth_middle': 1,
+           'use_linear_in_transformer': True, 'context_dim': 64, 'num_head_channels': 64,
+           'transformer_depth_output': [1, 1, 1, 1], 'use_temporal_attention': False, 'use_temporal_resblock': False}
+    unet = ref_unet.UNetModel(**cfg, device="cpu", dtype=torch.float32, operations=comfy.ops.disable_weight_init).eval()
+    _fill(unet, 21)
+    x, t, ctx = randn((2, 4, 32, 32), 1), torch.tensor([500.0, 20.0]), randn((2, 77, 64), 2)
+    with torch.inference_mode():
+        want = unet(x, t, context=ctx, transformer_options={})
+        with fake_native.patched() as calls:
+            integration.install()
+            try:
+                got = unet(x, t, context=ctx, transformer_options={})
+                again = unet(x, t, context=ctx, transformer_options={})      # weights now channels-last, caches warm
+            finally:
+                integration.uninstall()
+        after = unet(x, t, context=ctx, transformer_options={})            # the reference again, on the converted weights
+    assert calls["conv3x3"] >= 8 and calls.get("upsample2x_conv3x3", 0) >= 2 and calls["cat_channels"] >= 8, dict(calls)
+    assert unet.input_blocks[1][0].in_layers[2].weight.is_contiguous(memory_format=torch.channels_last)
+    scale = float(want.abs().max())
+    assert (got - want).abs().max() < 2e-4 * scale and (again - want).abs().max() < 2e-4 * scale
+    assert (after - want).abs().max() < 2e-4 * scale
+
+
+def test_vae_decoder_path_on_the_cpu_equals_the_reference(reference_tree):
+    """vae_path's host logic (channels-last conversion, bias / `x + h` folded into the convolutions, interpolate + conv,
+    the mid-block attention as q k^T -> row softmax -> . v on the GEMM entry points) with torch stand-ins on the CPU,
+    against the reference's own Decoder.forward."""
+    import comfy.ldm.modules.diffusionmodules.model as vm
+    import fake_native
+    from comfy_gen_server_b200 import integration
+    dd = {'double_z': True, 'z_channels': 4, 'resolution': 32, 'in_channels': 3, 'out_ch': 3, 'ch': 32,
+          'ch_mult': [1, 2], 'num_res_blocks': 1, 'attn_resolutions': [], 'dropout': 0.0}
+    dec = vm.Decoder(**dd).eval()
+    _fill(dec, 22)
+    z = randn((2, 4, 16, 16), 3)
+    with torch.inference_mode():
+        want = dec(z)
+        with fake_native.patched() as calls:
+            integration.install()
+            try:
+                got = dec(z)
+            finally:
+                integration.uninstall()
+    assert calls["conv3x3"] >= 6 and calls["upsample2x_conv3x3"] == 1 and calls["softmax_rows"] == 2, dict(calls)
+    assert calls["linear"] == 1 + 2 * 3, dict(calls)              # one fused q / k / v; per image: scores, . v, proj_out (+ x)
+    assert (got - want).abs().max() < 2e-4 * float(want.abs().max())
